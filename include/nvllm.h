@@ -1,0 +1,218 @@
+/*
+ * nvllm.h — C ABI of the B200-native (sm_100a) paged-attention decode hot path.
+ *
+ * This is the drop-in boundary for ssvgopal/nano-vllm-rs.  The reference has no FFI of its own
+ * (pure Rust on candle); each entry point below replaces one Rust method on the hot path and cites
+ * it as  <file>:<lines>  relative to the reference tree.  The Rust-side binding a maintainer
+ * would add is shown in INTEGRATION.md and rust/ffi.rs.
+ *
+ * Conventions (all entry points):
+ *   - return 0 on success, <0 for an argument error (shape / alignment / dtype), >0 = cudaError_t;
+ *     nvllm_last_error() returns a thread-local message for the last non-zero return.
+ *   - the caller owns every buffer (inputs, outputs, KV cache, workspace) and the stream; kernels
+ *     never allocate, free or synchronise and keep no global state, so every call is legal inside
+ *     CUDA-graph capture.  Pointers are device pointers unless the name starts with `h_`.
+ *   - activations / weights / KV cache are bf16 (NVLLM_BF16); accumulation is fp32.
+ *   - strides are in ELEMENTS.  The innermost (head_dim) dimension is always contiguous and every
+ *     row start must be 16-byte aligned.
+ *   - `stream` is a cudaStream_t passed as void*.
+ */
+#ifndef NVLLM_H_
+#define NVLLM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NVLLM_VERSION 100 /* 0.1.0 */
+
+enum nvllm_dtype { NVLLM_BF16 = 0, NVLLM_F32 = 1 };
+
+enum nvllm_status {
+  NVLLM_OK = 0,
+  NVLLM_ERR_ARG = -1,       /* bad shape / null pointer / unsupported size */
+  NVLLM_ERR_ALIGN = -2,     /* pointer or stride not 16-byte aligned        */
+  NVLLM_ERR_DTYPE = -3,     /* dtype other than the documented one          */
+  NVLLM_ERR_WORKSPACE = -4, /* workspace too small                          */
+  NVLLM_ERR_STATE = -5,     /* engine-level call in the wrong state         */
+  NVLLM_ERR_COMM = -6       /* NCCL / peer-memory failure                   */
+};
+
+int nvllm_version(void);
+const char* nvllm_last_error(void);
+/* 1 when a CUDA device of compute capability 10.x is visible, else 0 (never throws). */
+int nvllm_device_ok(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * KV-cache layout descriptor.  The reference allocates each per-layer cache as
+ * [num_blocks, block_size, num_kv_heads, head_dim]  (src/engine/model_runner.rs:379-389); that is
+ *   block_stride = block_size*Hkv*D, token_stride = Hkv*D, head_stride = D.
+ * The engine in this repo uses the head-major variant [num_blocks, Hkv, block_size, D]
+ *   block_stride = Hkv*block_size*D, token_stride = D, head_stride = block_size*D
+ * (64 KiB contiguous per (block, head)).  Kernels accept either through these strides.
+ * slot s  ->  block s / block_size, offset s % block_size   (slot_mapping semantics of
+ * src/layers/attention.rs:150-174 with a flat [num_blocks*block_size, ...] view).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct nvllm_kv_layout {
+  int32_t block_size;    /* tokens per block (reference: 256, src/config.rs:94)           */
+  int32_t num_kv_heads;  /* KV heads held by this rank (Hkv / tp)                           */
+  int32_t head_dim;      /* 64 or 128                                                       */
+  int32_t reserved;
+  int64_t block_stride;  /* elements between consecutive blocks                            */
+  int64_t token_stride;  /* elements between consecutive tokens inside a block             */
+  int64_t head_stride;   /* elements between consecutive KV heads of one token             */
+} nvllm_kv_layout;
+
+/* K1 — replaces Attention::store_kv_cache (src/layers/attention.rs:150-174).
+ * cache[slot_mapping[i]] = k[i], v[i] for i in [0, num_tokens); slot < 0 is skipped (padding rows
+ * of a captured decode graph).  k, v: [num_tokens, Hkv, D] with `kv_token_stride` elements between
+ * tokens (so they may be views into a packed qkv buffer).  Bit-exact copy. */
+int nvllm_store_kvcache(const void* k, const void* v, void* k_cache, void* v_cache,
+                        const int32_t* slot_mapping, int32_t num_tokens, int64_t kv_token_stride,
+                        const nvllm_kv_layout* layout, int32_t dtype, void* stream);
+
+/* K2 — replaces Attention::flash_attention_decode -> compute_attention_with_cache ->
+ * gather_cached_kv -> compute_attention (src/layers/attention.rs:225-318,238-261).
+ * out[b,h,:] = softmax(scale * q[b,h,:] . K[b,h/g]^T) . V[b,h/g] over the first context_lens[b]
+ * slots of the blocks listed in block_tables[b,:] (entries < 0 are skipped, attention.rs:306).
+ * q/out: [batch, H, D] with `q_token_stride` / `out_token_stride` elements between sequences.
+ * block_tables: i32 [batch, max_blocks_per_seq] padded with -1 (model_runner.rs:280-293);
+ * context_lens: i32 [batch] (model_runner.rs:275).  Split-K: `num_splits` >= 1 partitions of the
+ * KV length per (sequence, kv head); 0 lets the library choose.  Workspace holds the fp32 partials
+ * (only touched when the effective split count is > 1). */
+size_t nvllm_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t head_dim,
+                                          int32_t num_splits);
+int nvllm_paged_decode_choose_splits(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                                     int32_t max_context_len);
+int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache, const void* v_cache,
+                                 const int32_t* block_tables, const int32_t* context_lens,
+                                 int32_t batch, int32_t num_heads, int32_t max_blocks_per_seq,
+                                 int64_t q_token_stride, int64_t out_token_stride,
+                                 const nvllm_kv_layout* layout, float scale, void* workspace,
+                                 size_t workspace_bytes, int32_t num_splits, int32_t dtype,
+                                 void* stream);
+
+/* K3 / K4 — replaces Attention::flash_attention_varlen (+ create_causal_mask) and
+ * flash_attention_varlen_with_cache (src/layers/attention.rs:177-222,321-339).
+ * Causal attention per sequence i over q rows [cu_seqlens_q[i], cu_seqlens_q[i+1]) and keys
+ * [cu_seqlens_k[i], cu_seqlens_k[i+1]); the mask is bottom-right aligned (query row j of Lq sees
+ * keys 0 .. Lk-Lq+j), which is the plain causal mask when Lq == Lk.
+ * If block_tables == NULL keys/values come from the dense k, v: [total_k, Hkv, D];
+ * otherwise (prefix-cache prefill) they are read from the paged cache through block_tables[i,:]
+ * (the new K/V of this step must already have been stored — note N2 in SURVEY.md §8). */
+int nvllm_varlen_prefill_attention(void* out, const void* q, const void* k, const void* v,
+                                   const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                                   int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                                   int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                                   int64_t q_token_stride, int64_t kv_token_stride,
+                                   int64_t out_token_stride, const void* k_cache,
+                                   const void* v_cache, const int32_t* block_tables,
+                                   int32_t max_blocks_per_seq, const nvllm_kv_layout* layout,
+                                   float scale, int32_t dtype, void* stream);
+
+/* K5 — replaces LinearBase::forward of ReplicatedLinear / ColumnParallelLinear / RowParallelLinear /
+ * QKVParallelLinear / MergedColumnParallelLinear and ParallelLMHead::compute_logits
+ * (src/layers/linear.rs:228-239,354-356,437-439; src/layers/embed_head.rs:292-306).
+ * y[M,N] = x[M,K] . w[N,K]^T   (x, w bf16 row-major with leading dimensions ldx, ldw; fp32
+ * accumulate on tcgen05 tensor cores; y is bf16 or fp32 per `out_dtype`, leading dimension ldy).
+ * K % 64 == 0, N % 8 == 0, ldx/ldw % 8 == 0.  workspace: nvllm_gemm_workspace_bytes() bytes
+ * (TMA descriptors are passed by value, the workspace is only used for split-K partials; may be
+ * NULL when that function returns 0). */
+size_t nvllm_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
+int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
+                    int64_t ldx, int64_t ldw, int64_t ldy, int32_t out_dtype, void* workspace,
+                    size_t workspace_bytes, void* stream);
+/* Plain CUDA-core version of the same contract; test infrastructure for the kernel above (used to
+ * check large shapes on the device where the CPU oracle is too slow).  Never on the product path. */
+int nvllm_gemm_bf16_simt(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
+                         int64_t ldx, int64_t ldw, int64_t ldy, int32_t out_dtype, void* stream);
+
+/* K6 — replaces RMSNorm::forward_simple / forward_with_residual (src/layers/layernorm.rs:58-97)
+ * and the residual adds of Qwen3Layer::forward (src/models/qwen3.rs:382,389).
+ *   residual == NULL : out = rmsnorm(x) * w
+ *   residual != NULL : residual <- bf16(residual + x) (in place);  out = rmsnorm(residual) * w
+ * f32 math: v * w / sqrt(mean(v^2) + eps).  x/out: [num_tokens, hidden], contiguous rows. */
+int nvllm_add_rmsnorm(void* out, const void* x, void* residual, const void* weight,
+                      int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream);
+
+/* K7 (+K1 fused) — replaces RotaryEmbedding::forward / apply_rotary_emb_single
+ * (src/layers/rotary_embedding.rs:23-48,136-158), the per-head q_norm/k_norm of the named Qwen3
+ * architecture (absent in the reference, SURVEY.md §8 note N1) and, when k_cache != NULL, the
+ * store_kv_cache call that follows (attention.rs:78-81).
+ * In place on the packed qkv buffer [num_tokens, (H + 2*Hkv) * D] (q | k | v, linear.rs:331-340):
+ *   q_h <- rope(rmsnorm_D(q_h) * q_norm_w),  k_h <- rope(rmsnorm_D(k_h) * k_norm_w)
+ *   rope: half-split (NeoX) rotation [x1*c - x2*s | x2*c + x1*s], c,s = cos,sin(pos * theta^(-2j/D))
+ *   taken from the fp32 table cos_sin: [max_position, D] = (cos[0..D/2) | sin[0..D/2)).
+ * q_norm_w / k_norm_w may be NULL (no qk-norm: the reference's behaviour).  positions: i64. */
+int nvllm_qknorm_rope_store(void* qkv, const int64_t* positions, const float* cos_sin,
+                            const void* q_norm_w, const void* k_norm_w, float eps,
+                            int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads,
+                            int32_t head_dim, int32_t max_position, void* k_cache, void* v_cache,
+                            const int32_t* slot_mapping, const nvllm_kv_layout* layout,
+                            int32_t dtype, void* stream);
+/* Fills cos_sin [max_position, D] fp32 exactly as the oracle does (f64 inv_freq and angle, rounded
+ * to f32) — rotary_embedding.rs:82-110 with the table kept in f32 (note N1). */
+int nvllm_rope_table(float* cos_sin, int32_t max_position, int32_t head_dim, double theta,
+                     void* stream);
+
+/* K8 — replaces SiluAndMul::forward (src/layers/activation.rs:46-63).
+ * out[t, j] = silu(x[t, j]) * x[t, inter + j],  x: [num_tokens, 2*inter], out: [num_tokens, inter]. */
+int nvllm_silu_mul(void* out, const void* x, int32_t num_tokens, int32_t inter, int32_t dtype,
+                   void* stream);
+
+/* K9 / K10 — replaces VocabParallelEmbedding::forward (src/layers/embed_head.rs:77-97) and
+ * ParallelLMHead::extract_last_tokens (embed_head.rs:272-289).
+ * gather rows: out[i,:] = table[ids[i],:]  (ids i64).  With `row_index` semantic = last token of each
+ * sequence use nvllm_gather_last_tokens: out[i,:] = x[cu_seqlens_q[i+1]-1, :]. */
+int nvllm_embedding_gather(void* out, const void* table, const int64_t* ids, int32_t num_tokens,
+                           int32_t hidden, int32_t vocab, int32_t dtype, void* stream);
+int nvllm_gather_last_tokens(void* out, const void* x, const int32_t* cu_seqlens_q, int32_t batch,
+                             int32_t hidden, int32_t dtype, void* stream);
+
+/* K11 — replaces Sampler::greedy_sample (src/layers/sampler.rs:109-112): argmax over the vocab,
+ * first maximum wins.  logits: [batch, vocab] (bf16 or f32, leading dimension ld).  Writes the token
+ * id (+ vocab_offset, for vocab-sharded heads) to out_ids[b] (i64) and, if out_max != NULL, the
+ * maximum as f32 to out_max[b] (used for the cross-rank combine, embed_head.rs:321-336). */
+int nvllm_argmax(int64_t* out_ids, float* out_max, const void* logits, int32_t batch, int32_t vocab,
+                 int64_t ld, int64_t vocab_offset, int32_t logits_dtype, void* stream);
+/* Cross-rank combine of per-shard (max, id) pairs gathered as [tp, batch]: picks the largest max,
+ * lowest shard on ties (== first maximum over the concatenated vocab). */
+int nvllm_argmax_combine(int64_t* out_ids, const float* all_max, const int64_t* all_ids,
+                         int32_t tp, int32_t batch, void* stream);
+
+/* C1 — the all-reduce the reference leaves as a TODO after o_proj / down_proj
+ * (src/layers/linear.rs:236).  One communicator per process (one process per GPU).
+ * nvllm_comm_unique_id writes NVLLM_UNIQUE_ID_BYTES bytes on rank 0; the caller broadcasts them
+ * (torch.distributed / any transport) and every rank calls nvllm_comm_init. */
+#define NVLLM_UNIQUE_ID_BYTES 128
+typedef struct nvllm_comm nvllm_comm;
+int nvllm_comm_unique_id(void* h_id_out);
+int nvllm_comm_init(nvllm_comm** comm, const void* h_id, int32_t rank, int32_t world);
+int nvllm_comm_destroy(nvllm_comm* comm);
+/* In-place sum over ranks of buf[count] (bf16 or f32), enqueued on `stream` (graph-capturable). */
+int nvllm_allreduce(nvllm_comm* comm, void* buf, size_t count, int32_t dtype, void* stream);
+int nvllm_allgather(nvllm_comm* comm, const void* send, void* recv, size_t bytes_per_rank,
+                    void* stream);
+
+/* Deterministic seeded weight init shared bit-for-bit with the CPU oracle (oracle/weights.py):
+ * element i of tensor `tensor_id` = bf16( (sum of the four 16-bit fields of
+ * splitmix64(seed ^ tensor_id<<40, i)  - 131070) * std_scale ).  Integer arithmetic + one exact
+ * int->f32 multiply, so host and device agree bit-exactly. */
+int nvllm_init_weight(void* w, int64_t count, uint64_t seed, uint64_t tensor_id, float std,
+                      int32_t dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Engine-level C ABI: the C++ host runtime that mirrors the reference's Rust types one-to-one
+ * (Config, SamplingParams, Sequence, BlockManager, Scheduler, ModelRunner, Qwen3Model, LLMEngine).
+ * Declared in nvllm_engine.h; kept separate so a Rust caller that only wants the kernels binds
+ * this header alone.
+ * ---------------------------------------------------------------------------------------------- */
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+#endif /* NVLLM_H_ */

@@ -1,0 +1,436 @@
+// paged_decode.cu — K2: split-K paged decode attention for GQA heads (HBM-bound).
+//
+// Replaces Attention::flash_attention_decode -> compute_attention_with_cache -> gather_cached_kv ->
+// compute_attention (reference src/layers/attention.rs:225-318,238-261): the reference walks
+// block_tables on the host, concatenates whole KV blocks (a full copy of the context) and runs a
+// dense matmul + softmax per sequence.  Here every KV byte is read from HBM exactly once.
+//
+// Work decomposition
+//   grid = (num_splits, Hkv * ceil(g/8), batch); one CTA owns one (sequence, kv head, q-head group of
+//   <= 8, split of the KV length).  A CTA iterates over tiles of 16*NWARPS consecutive tokens; warp w
+//   owns rows [16w, 16w+16) of every tile and runs its own cp.async pipeline (STAGES deep, 8 KiB per
+//   stage for D=128), so the main loop contains no block-level barrier at all.
+// Staging
+//   cp.async (LDGSTS) 16-byte copies, global -> shared, XOR-swizzled on the 16-byte chunk index so the
+//   ldmatrix reads are bank-conflict free.  Rows past context_lens are zero-filled.
+// Math (per warp, per 16 tokens), transposed so that the GQA group sits on the MMA N dimension:
+//   S^T[16 tok x 8 heads] = K[16 x D] . Q^T[D x 8]          (mma.sync m16n8k16, A = K via ldmatrix)
+//   online softmax over tokens: quad/warp shuffles (xor 4,8,16), exp2 with scale*log2(e) folded in
+//   P^T -> B operand through movmatrix.trans (8x8 b16 transpose inside the warp)
+//   O^T[D x 8 heads] += V^T[D x 16 tok] . P^T[16 x 8]        (A = V via ldmatrix.trans)
+//   No padding waste for g = 8, 2x for g = 4, 4x for g = 2 — the tensor pipe is idle otherwise.
+// Epilogue: warps merge (m, l, O) through shared memory; with one split the CTA writes bf16 output,
+//   otherwise fp32 partials + (m, l) go to the workspace and paged_decode_reduce_kernel combines.
+//
+// Algorithmic bytes per launch: sum_b 2*L_b*Hkv*D*2 + 2*B*H*D*2 + 4*sum_b ceil(L_b/bs) + 4*B.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace nvllm {
+
+int check_layout(const nvllm_kv_layout* L);  // store_kvcache.cu
+
+struct DecodeParams {
+  bf16* out;
+  const bf16* q;
+  const bf16* kc;
+  const bf16* vc;
+  const int32_t* tables;
+  const int32_t* ctx;
+  float* ws_o;   // [B, H, S, D]
+  float* ws_ml;  // [B, H, S, 2]
+  int batch, H, Hkv, g, ngrp, max_blocks, block_size, num_splits;
+  int64_t q_stride, out_stride, blk_stride, tok_stride, head_stride;
+  float scale_log2;
+};
+
+template <int D, int STAGES, int NWARPS>
+struct DecodeCfg {
+  static constexpr int kChunks = D / 8;                // 16-byte chunks per row
+  static constexpr int kRowBytes = D * 2;
+  static constexpr int kSubTileBytes = 16 * kRowBytes;  // 16 tokens of K (or V)
+  static constexpr int kStageBytes = 2 * kSubTileBytes; // K + V
+  static constexpr int kWarpBytes = STAGES * kStageBytes;
+  static constexpr int kPipeBytes = NWARPS * kWarpBytes;
+  static constexpr int kOStride = D + 4;                // fp32 words per head row in the merge buffer
+  static constexpr int kMergeBytes = NWARPS * (8 * kOStride + 16) * 4;
+  static constexpr int kSmemBytes = kPipeBytes > kMergeBytes ? kPipeBytes : kMergeBytes;
+  static constexpr int kRowsPerLane = 16 * kChunks / 32;  // cp.async per lane per K sub-tile
+  static constexpr int kRowStep = 32 / kChunks;
+};
+
+template <int D, int STAGES, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32, (DecodeCfg<D, STAGES, NWARPS>::kSmemBytes <= 110 * 1024) ? 2 : 1)
+paged_decode_kernel(const DecodeParams p) {
+  using C = DecodeCfg<D, STAGES, NWARPS>;
+  constexpr int KS = D / 16;  // k-steps of QK^T == m-tiles of PV
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int split = blockIdx.x;
+  const int kvh = blockIdx.y / p.ngrp;
+  const int grp = blockIdx.y - kvh * p.ngrp;
+  const int b = blockIdx.z;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int ctx = __ldg(p.ctx + b);
+  const int gvalid = min(8, p.g - grp * 8);   // q heads handled by this CTA
+  const int qh0 = kvh * p.g + grp * 8;         // first q head
+
+  constexpr int TILE = 16 * NWARPS;
+  const int tiles_total = (ctx + TILE - 1) / TILE;
+  const int tps = (tiles_total + p.num_splits - 1) / p.num_splits;
+  const int t0 = split * tps;
+  const int t1 = min(t0 + tps, tiles_total);
+  const int n = max(t1 - t0, 0);
+
+  // ---- Q^T B-fragments: head n = lane/4, dims 16ks + 2(lane%4) + {0,1} (+8) --------------------
+  uint32_t qb[KS][2];
+  {
+    const int hn = lane >> 2;
+    const bool hv = hn < gvalid;
+    const bf16* qrow = p.q + b * p.q_stride + static_cast<int64_t>(qh0 + (hv ? hn : 0)) * D;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int d0 = ks * 16 + (lane & 3) * 2;
+      qb[ks][0] = hv ? *reinterpret_cast<const uint32_t*>(qrow + d0) : 0u;
+      qb[ks][1] = hv ? *reinterpret_cast<const uint32_t*>(qrow + d0 + 8) : 0u;
+    }
+  }
+
+  const uint32_t warp_smem = smem_u32(smem) + warp * C::kWarpBytes;
+  const int32_t* table = p.tables + static_cast<int64_t>(b) * p.max_blocks;
+  const bf16* kbase = p.kc + kvh * p.head_stride;
+  const bf16* vbase = p.vc + kvh * p.head_stride;
+
+  auto issue = [&](int i) {
+    const int s = i % STAGES;
+    const int tok_base = ((t0 + i) * NWARPS + warp) * 16;
+    int blk = -1, off = 0;
+    if (tok_base < ctx) {
+      const int bi = tok_base / p.block_size;
+      off = tok_base - bi * p.block_size;
+      if (bi < p.max_blocks) blk = __ldg(table + bi);
+    }
+    const uint32_t sK = warp_smem + s * C::kStageBytes;
+    const uint32_t sV = sK + C::kSubTileBytes;
+    const int c = lane % C::kChunks;
+    const int r0 = lane / C::kChunks;
+    const int64_t gofs0 = static_cast<int64_t>(blk < 0 ? 0 : blk) * p.blk_stride + c * 8;
+#pragma unroll
+    for (int j = 0; j < C::kRowsPerLane; ++j) {
+      const int r = r0 + j * C::kRowStep;
+      const bool valid = (blk >= 0) && (tok_base + r < ctx);
+      const int64_t gofs = valid ? gofs0 + static_cast<int64_t>(off + r) * p.tok_stride : 0;
+      const uint32_t dst = r * C::kRowBytes + ((c ^ (r & 7)) << 4);
+      cp_async_16(sK + dst, kbase + gofs, valid ? 16 : 0);
+      cp_async_16(sV + dst, vbase + gofs, valid ? 16 : 0);
+    }
+  };
+
+  float m_run[2] = {-INFINITY, -INFINITY};
+  float l_run[2] = {0.f, 0.f};
+  float acc[KS][4];
+#pragma unroll
+  for (int mt = 0; mt < KS; ++mt) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0.f;
+
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (s < n) issue(s);
+    cp_async_commit();
+  }
+
+  for (int i = 0; i < n; ++i) {
+    cp_async_wait<STAGES - 2>();
+    __syncwarp();
+    if (i + STAGES - 1 < n) issue(i + STAGES - 1);
+    cp_async_commit();
+
+    const int s = i % STAGES;
+    const uint32_t sK = warp_smem + s * C::kStageBytes;
+    const uint32_t sV = sK + C::kSubTileBytes;
+    const int tok_base = ((t0 + i) * NWARPS + warp) * 16;
+    const int mat = lane >> 3;
+    const int sw = lane & 7;
+
+    // ---- S^T = K . Q^T --------------------------------------------------------------------------
+    float sacc[4] = {0.f, 0.f, 0.f, 0.f};
+    {
+      const int r = sw + (mat & 1) * 8;
+      const uint32_t rowaddr = sK + r * C::kRowBytes;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        uint32_t a[4];
+        const int c = 2 * ks + (mat >> 1);
+        ldmatrix_x4(a, rowaddr + ((c ^ sw) << 4));
+        mma_bf16_16816(sacc, a, qb[ks][0], qb[ks][1]);
+      }
+    }
+
+    // ---- online softmax over tokens (rows of S^T): lanes sharing lane%4 hold the same heads ------
+    const int tokA = tok_base + (lane >> 2);
+    float s0 = sacc[0] * p.scale_log2, s1 = sacc[1] * p.scale_log2;
+    float s2 = sacc[2] * p.scale_log2, s3 = sacc[3] * p.scale_log2;
+    if (tokA >= ctx) s0 = s1 = -INFINITY;
+    if (tokA + 8 >= ctx) s2 = s3 = -INFINITY;
+    float mx0 = fmaxf(s0, s2), mx1 = fmaxf(s1, s3);
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, o));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, o));
+    }
+    const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+    const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0, ms1 = (mn1 == -INFINITY) ? 0.f : mn1;
+    const float corr0 = fast_exp2(m_run[0] - ms0), corr1 = fast_exp2(m_run[1] - ms1);
+    const float p0 = fast_exp2(s0 - ms0), p1 = fast_exp2(s1 - ms1);
+    const float p2 = fast_exp2(s2 - ms0), p3 = fast_exp2(s3 - ms1);
+    l_run[0] = l_run[0] * corr0 + p0 + p2;
+    l_run[1] = l_run[1] * corr1 + p1 + p3;
+    m_run[0] = mn0;
+    m_run[1] = mn1;
+    const uint32_t pb0 = movmatrix_trans(pack_bf16x2(p0, p1));  // tokens 0-7  -> B rows k
+    const uint32_t pb1 = movmatrix_trans(pack_bf16x2(p2, p3));  // tokens 8-15
+
+    // ---- O^T += V^T . P^T -------------------------------------------------------------------------
+    {
+      const int r = sw + (mat >> 1) * 8;
+      const uint32_t rowaddr = sV + r * C::kRowBytes;
+      const bool rescale = __any_sync(0xffffffffu, (corr0 != 1.f) || (corr1 != 1.f));
+#pragma unroll
+      for (int mt = 0; mt < KS; ++mt) {
+        if (rescale) {
+          acc[mt][0] *= corr0;
+          acc[mt][1] *= corr1;
+          acc[mt][2] *= corr0;
+          acc[mt][3] *= corr1;
+        }
+        uint32_t a[4];
+        const int c = 2 * mt + (mat & 1);
+        ldmatrix_x4_trans(a, rowaddr + ((c ^ sw) << 4));
+        mma_bf16_16816(acc[mt], a, pb0, pb1);
+      }
+    }
+  }
+
+  // ---- merge the NWARPS partial states through shared memory ------------------------------------
+  cp_async_wait<0>();
+#pragma unroll
+  for (int o = 4; o < 32; o <<= 1) {
+    l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], o);
+    l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], o);
+  }
+  __syncthreads();  // every warp is done with its pipeline buffers
+  float* so = reinterpret_cast<float*>(smem);                   // [NWARPS][8][kOStride]
+  float* sml = so + NWARPS * 8 * C::kOStride;                   // [NWARPS][8][2]
+  {
+    const int h0 = (lane & 3) * 2;
+    float* sw_o = so + warp * 8 * C::kOStride;
+#pragma unroll
+    for (int mt = 0; mt < KS; ++mt) {
+      const int d = mt * 16 + (lane >> 2);
+      sw_o[h0 * C::kOStride + d] = acc[mt][0];
+      sw_o[(h0 + 1) * C::kOStride + d] = acc[mt][1];
+      sw_o[h0 * C::kOStride + d + 8] = acc[mt][2];
+      sw_o[(h0 + 1) * C::kOStride + d + 8] = acc[mt][3];
+    }
+    if (lane < 4) {
+      float* w_ml = sml + warp * 16;
+      w_ml[h0 * 2 + 0] = m_run[0];
+      w_ml[h0 * 2 + 1] = l_run[0];
+      w_ml[(h0 + 1) * 2 + 0] = m_run[1];
+      w_ml[(h0 + 1) * 2 + 1] = l_run[1];
+    }
+  }
+  __syncthreads();
+
+  for (int idx = threadIdx.x; idx < gvalid * D; idx += NWARPS * 32) {
+    const int hn = idx / D;
+    const int d = idx - hn * D;
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < NWARPS; ++w) M = fmaxf(M, sml[w * 16 + hn * 2]);
+    float o = 0.f, L = 0.f;
+    if (M != -INFINITY) {
+#pragma unroll
+      for (int w = 0; w < NWARPS; ++w) {
+        const float mw = sml[w * 16 + hn * 2];
+        const float f = (mw == -INFINITY) ? 0.f : fast_exp2(mw - M);
+        o += so[(w * 8 + hn) * C::kOStride + d] * f;
+        L += sml[w * 16 + hn * 2 + 1] * f;
+      }
+    }
+    const int qh = qh0 + hn;
+    if (p.num_splits == 1) {
+      p.out[b * p.out_stride + static_cast<int64_t>(qh) * D + d] =
+          __float2bfloat16_rn(L > 0.f ? o / L : 0.f);
+    } else {
+      const int64_t slot = (static_cast<int64_t>(b) * p.H + qh) * p.num_splits + split;
+      p.ws_o[slot * D + d] = o;
+      if (d == 0) {
+        p.ws_ml[slot * 2 + 0] = M;
+        p.ws_ml[slot * 2 + 1] = L;
+      }
+    }
+  }
+}
+
+// Combines the split-K partials: grid (H, B), D threads.
+template <int D>
+__global__ void __launch_bounds__(D) paged_decode_reduce_kernel(const DecodeParams p) {
+  const int qh = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
+  const int64_t base = (static_cast<int64_t>(b) * p.H + qh) * p.num_splits;
+  float M = -INFINITY;
+  for (int s = 0; s < p.num_splits; ++s) M = fmaxf(M, __ldg(p.ws_ml + (base + s) * 2));
+  float o = 0.f, L = 0.f;
+  if (M != -INFINITY) {
+    for (int s = 0; s < p.num_splits; ++s) {
+      const float ms = __ldg(p.ws_ml + (base + s) * 2);
+      if (ms == -INFINITY) continue;
+      const float f = fast_exp2(ms - M);
+      o += p.ws_o[(base + s) * D + d] * f;
+      L += __ldg(p.ws_ml + (base + s) * 2 + 1) * f;
+    }
+  }
+  p.out[b * p.out_stride + static_cast<int64_t>(qh) * D + d] = __float2bfloat16_rn(L > 0.f ? o / L : 0.f);
+}
+
+}  // namespace nvllm
+
+// ------------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------------
+namespace nvllm {
+
+template <int D, int STAGES, int NWARPS>
+static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
+  using C = DecodeCfg<D, STAGES, NWARPS>;
+  auto kern = paged_decode_kernel<D, STAGES, NWARPS>;
+  static bool attr_set = false;  // per instantiation; idempotent, so a race only repeats the call
+  if (!attr_set) {
+    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_set = true;
+  }
+  dim3 grid(p.num_splits, p.Hkv * p.ngrp, p.batch);
+  kern<<<grid, NWARPS * 32, C::kSmemBytes, stream>>>(p);
+  NVLLM_LAUNCH_CHECK("paged_decode_kernel");
+  if (p.num_splits > 1) {
+    paged_decode_reduce_kernel<D><<<dim3(p.H, p.batch), D, 0, stream>>>(p);
+    NVLLM_LAUNCH_CHECK("paged_decode_reduce_kernel");
+  }
+  return 0;
+}
+
+// Tuning knob for benchmarking only (bench.py --decode-cfg): 0 = default.
+static int decode_cfg_id() {
+  static int id = -1;
+  if (id < 0) {
+    const char* e = getenv("NVLLM_DECODE_CFG");
+    id = e ? atoi(e) : 0;
+  }
+  return id;
+}
+
+}  // namespace nvllm
+
+extern "C" size_t nvllm_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads,
+                                                     int32_t head_dim, int32_t num_splits) {
+  if (batch <= 0 || num_heads <= 0 || head_dim <= 0) return 0;
+  if (num_splits <= 0) num_splits = 64;  // upper bound of nvllm_paged_decode_choose_splits
+  if (num_splits == 1) return 0;
+  const size_t slots = static_cast<size_t>(batch) * num_heads * num_splits;
+  return slots * head_dim * sizeof(float) + slots * 2 * sizeof(float);
+}
+
+extern "C" int nvllm_paged_decode_choose_splits(int32_t batch, int32_t num_heads,
+                                                int32_t num_kv_heads, int32_t max_context_len) {
+  if (batch <= 0 || num_heads <= 0 || num_kv_heads <= 0) return 1;
+  const int g = num_heads / num_kv_heads;
+  const int ngrp = (g + 7) / 8;
+  const long base = static_cast<long>(batch) * num_kv_heads * ngrp;
+  const int sms = nvllm::sm_count();
+  if (base >= 2L * sms) return 1;
+  long want = (3L * sms + base - 1) / base;        // ~3 CTAs per SM
+  long by_len = max_context_len / 256;             // keep >= 256 tokens per split
+  if (by_len < 1) by_len = 1;
+  if (want > by_len) want = by_len;
+  if (want > 64) want = 64;
+  if (want < 1) want = 1;
+  return static_cast<int>(want);
+}
+
+extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache,
+                                            const void* v_cache, const int32_t* block_tables,
+                                            const int32_t* context_lens, int32_t batch,
+                                            int32_t num_heads, int32_t max_blocks_per_seq,
+                                            int64_t q_token_stride, int64_t out_token_stride,
+                                            const nvllm_kv_layout* layout, float scale,
+                                            void* workspace, size_t workspace_bytes,
+                                            int32_t num_splits, int32_t dtype, void* stream) {
+  using namespace nvllm;
+  NVLLM_CHECK_ARG(dtype == NVLLM_BF16, NVLLM_ERR_DTYPE, "paged_decode: dtype %d (bf16 only)", dtype);
+  if (int rc = check_layout(layout)) return rc;
+  NVLLM_CHECK_ARG(batch >= 0 && batch <= 65535, NVLLM_ERR_ARG, "paged_decode: batch %d", batch);
+  if (batch == 0) return 0;
+  const int Hkv = layout->num_kv_heads, D = layout->head_dim;
+  NVLLM_CHECK_ARG(num_heads > 0 && num_heads % Hkv == 0, NVLLM_ERR_ARG,
+                  "paged_decode: num_heads %d not a multiple of num_kv_heads %d", num_heads, Hkv);
+  NVLLM_CHECK_ARG(layout->block_size % 16 == 0, NVLLM_ERR_ARG,
+                  "paged_decode: block_size %d must be a multiple of 16", layout->block_size);
+  NVLLM_CHECK_ARG(max_blocks_per_seq > 0, NVLLM_ERR_ARG, "paged_decode: max_blocks_per_seq %d",
+                  max_blocks_per_seq);
+  NVLLM_CHECK_ARG(out && q && k_cache && v_cache && block_tables && context_lens, NVLLM_ERR_ARG,
+                  "paged_decode: NULL pointer");
+  NVLLM_CHECK_ARG(aligned16(out) && aligned16(q) && aligned16(k_cache) && aligned16(v_cache),
+                  NVLLM_ERR_ALIGN, "paged_decode: pointers must be 16-byte aligned");
+  NVLLM_CHECK_ARG(q_token_stride % 8 == 0 && out_token_stride % 8 == 0 &&
+                      q_token_stride >= static_cast<int64_t>(num_heads) * D &&
+                      out_token_stride >= static_cast<int64_t>(num_heads) * D,
+                  NVLLM_ERR_ALIGN, "paged_decode: q/out token stride");
+  const int g = num_heads / Hkv;
+  if (num_splits <= 0)
+    num_splits = nvllm_paged_decode_choose_splits(batch, num_heads, Hkv,
+                                                  max_blocks_per_seq * layout->block_size);
+  NVLLM_CHECK_ARG(num_splits <= 1024, NVLLM_ERR_ARG, "paged_decode: num_splits %d", num_splits);
+  DecodeParams p;
+  p.out = static_cast<bf16*>(out);
+  p.q = static_cast<const bf16*>(q);
+  p.kc = static_cast<const bf16*>(k_cache);
+  p.vc = static_cast<const bf16*>(v_cache);
+  p.tables = block_tables;
+  p.ctx = context_lens;
+  p.ws_o = nullptr;
+  p.ws_ml = nullptr;
+  if (num_splits > 1) {
+    const size_t need = nvllm_paged_decode_workspace_bytes(batch, num_heads, D, num_splits);
+    NVLLM_CHECK_ARG(workspace != nullptr && workspace_bytes >= need, NVLLM_ERR_WORKSPACE,
+                    "paged_decode: workspace %zu < %zu bytes", workspace_bytes, need);
+    NVLLM_CHECK_ARG(aligned16(workspace), NVLLM_ERR_ALIGN, "paged_decode: workspace alignment");
+    const size_t slots = static_cast<size_t>(batch) * num_heads * num_splits;
+    p.ws_o = static_cast<float*>(workspace);
+    p.ws_ml = p.ws_o + slots * D;
+  }
+  p.batch = batch;
+  p.H = num_heads;
+  p.Hkv = Hkv;
+  p.g = g;
+  p.ngrp = (g + 7) / 8;
+  p.max_blocks = max_blocks_per_seq;
+  p.block_size = layout->block_size;
+  p.num_splits = num_splits;
+  p.q_stride = q_token_stride;
+  p.out_stride = out_token_stride;
+  p.blk_stride = layout->block_stride;
+  p.tok_stride = layout->token_stride;
+  p.head_stride = layout->head_stride;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (D == 128) {
+    switch (decode_cfg_id()) {
+      case 1: return launch_decode<128, 4, 4>(p, st);
+      case 2: return launch_decode<128, 3, 8>(p, st);
+      case 3: return launch_decode<128, 2, 4>(p, st);
+      default: return launch_decode<128, 3, 4>(p, st);
+    }
+  }
+  return launch_decode<64, 4, 4>(p, st);
+}

@@ -1,0 +1,23 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session")
+def cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from nano_vllm_rs_b200 import _ffi
+    lib = _ffi.lib()  # raises if the extension is missing: GPU tests must never pass on a fallback
+    assert lib.nvllm_device_ok() == 1, "libnvllm.so loaded but no sm_100 device visible"
+    return torch.device("cuda:0")
