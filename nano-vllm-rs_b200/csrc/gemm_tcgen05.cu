@@ -1,0 +1,246 @@
+// gemm_tcgen05.cu — K5: y[M,N] = x[M,K] . w[N,K]^T, bf16 x bf16 -> fp32 on the 5th-gen tensor cores.
+//
+// Replaces candle_nn::Linear behind LinearBase::forward (reference src/layers/linear.rs:228-239,354-356,
+// 437-439) and ParallelLMHead::compute_logits (src/layers/embed_head.rs:292-306).
+//
+// Persistent, warp-specialised, one CTA per SM:
+//   warp 0 (one lane)  TMA producer: cp.async.bulk.tensor 2-D tiles of x (128 x 64) and w (BN x 64) into a
+//                      STAGES-deep shared-memory ring, SWIZZLE_128B, completion on `full` mbarriers
+//   warp 1 (one lane)  MMA issuer: tcgen05.mma.cta_group::1.kind::f16, M=128, N=BN, K=16 x4 per stage,
+//                      accumulators in TMEM (2 x BN columns, double buffered); tcgen05.commit releases
+//                      the smem stage (`empty`) and, after the last k-block, publishes the tile (`tmem_full`)
+//   warp 2             TMEM allocator
+//   warps 4-7          epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> bf16/fp32 -> 16-byte global
+//                      stores, overlapped with the next tile's MMAs through the second TMEM buffer
+// Both operands are K-major (row-major x and row-major w), the canonical TN case: no transposes anywhere.
+// Tiles are enumerated m-fastest so CTAs running together share the same w tile in L2; w is read from
+// HBM once.  M and N tails: TMA zero-fills out-of-bounds rows, the epilogue predicates its stores.
+#include "tc.cuh"
+
+namespace nvllm {
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int BM = 128, BK = 64;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (200 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int kBarBytes = (2 * kStages + 4) * 8 + 16;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+};
+
+template <typename OutT>
+__device__ __forceinline__ void store_row32(OutT* dst, const uint32_t (&r)[32], int col0, int n);
+
+template <>
+__device__ __forceinline__ void store_row32<bf16>(bf16* dst, const uint32_t (&r)[32], int col0, int n) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (col0 + j * 8 < n) {
+      uint4 v;
+      v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+      v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+      v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+      v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+      *reinterpret_cast<uint4*>(dst + j * 8) = v;
+    }
+  }
+}
+template <>
+__device__ __forceinline__ void store_row32<float>(float* dst, const uint32_t (&r)[32], int col0, int n) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (col0 + j * 4 < n) {
+      *reinterpret_cast<uint4*>(dst + j * 4) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+    }
+  }
+}
+
+template <int BN, typename OutT>
+__global__ void __launch_bounds__(256, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                    OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles) {
+  using C = GemmCfg<BN>;
+  constexpr int STAGES = C::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B tiles: 1024-byte aligned
+  const uint32_t sA = smem_base;
+  const uint32_t sB = smem_base + STAGES * C::kABytes;
+  const uint32_t bars = smem_base + STAGES * C::kStageBytes;
+  auto full_bar = [&](int s) { return bars + s * 8; };
+  auto empty_bar = [&](int s) { return bars + (STAGES + s) * 8; };
+  auto tfull_bar = [&](int a) { return bars + (2 * STAGES + a) * 8; };
+  auto tempty_bar = [&](int a) { return bars + (2 * STAGES + 2 + a) * 8; };
+  const uint32_t tmem_slot = bars + (2 * STAGES + 4) * 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_kb = K / C::BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        mbar_expect_tx(full_bar(stage), C::kStageBytes);
+        tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
+        tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer (single thread) =====
+    constexpr uint32_t idesc = umma_idesc_bf16(C::BM, BN, 0, 0);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1);  // epilogue has drained this TMEM buffer
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t a0 = sA + stage * C::kABytes, b0 = sB + stage * C::kBBytes;
+#pragma unroll
+        for (int k = 0; k < C::BK / 16; ++k) {
+          const uint64_t adesc = umma_desc_sw128(a0 + k * 32, 16, 1024);
+          const uint64_t bdesc = umma_desc_sw128(b0 + k * 32, 16, 1024);
+          umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(empty_bar(stage));                      // smem stage reusable once these MMAs retire
+        if (kb == num_kb - 1) umma_commit(tfull_bar(acc));  // accumulator complete
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: TMEM -> registers -> global =====
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const int row = m_tile * C::BM + q * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n_tile * BN + c * 32;
+        if (row < M && col0 < N) store_row32<OutT>(y + row * ldy + col0, r, col0, N);
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar(acc));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
+}
+
+template <int BN, typename OutT>
+static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy,
+                       cudaStream_t st) {
+  using C = GemmCfg<BN>;
+  auto kern = gemm_tcgen05_kernel<BN, OutT>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_set = true;
+  }
+  const int num_m_tiles = (M + C::BM - 1) / C::BM;
+  const int num_n_tiles = (N + BN - 1) / BN;
+  const int num_tiles = num_m_tiles * num_n_tiles;
+  const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
+  kern<<<grid, 256, C::kSmemBytes, st>>>(tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles);
+  NVLLM_LAUNCH_CHECK("gemm_tcgen05_kernel");
+  return 0;
+}
+
+static int pick_bn(int M, int N) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("NVLLM_GEMM_BN");  // benchmarking knob
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
+  const int sms = sm_count();
+  const long mt = (M + 127) / 128;
+  const int cands[4] = {256, 128, 64, 32};
+  for (int i = 0; i < 4; ++i) {
+    const long tiles = mt * ((N + cands[i] - 1) / cands[i]);
+    if (tiles >= sms) return cands[i];
+  }
+  return 32;
+}
+
+}  // namespace nvllm
+
+extern "C" size_t nvllm_gemm_workspace_bytes(int32_t, int32_t, int32_t) { return 0; }
+
+extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
+                               int64_t ldx, int64_t ldw, int64_t ldy, int32_t out_dtype, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  using namespace nvllm;
+  (void)workspace; (void)workspace_bytes;
+  NVLLM_CHECK_ARG(m >= 0 && n > 0 && k > 0, NVLLM_ERR_ARG, "gemm: m=%d n=%d k=%d", m, n, k);
+  NVLLM_CHECK_ARG(k % 64 == 0 && n % 8 == 0, NVLLM_ERR_ARG, "gemm: need k %% 64 == 0 and n %% 8 == 0 (k=%d n=%d)", k, n);
+  NVLLM_CHECK_ARG(ldx >= k && ldw >= k && ldy >= n && ldx % 8 == 0 && ldw % 8 == 0 && ldy % 8 == 0, NVLLM_ERR_ALIGN,
+                  "gemm: leading dimensions ldx=%lld ldw=%lld ldy=%lld", (long long)ldx, (long long)ldw, (long long)ldy);
+  NVLLM_CHECK_ARG(out_dtype == NVLLM_BF16 || out_dtype == NVLLM_F32, NVLLM_ERR_DTYPE, "gemm: out_dtype %d", out_dtype);
+  if (m == 0) return 0;
+  NVLLM_CHECK_ARG(y && x && w && aligned16(y) && aligned16(x) && aligned16(w), NVLLM_ERR_ALIGN, "gemm: pointers");
+  const int bn = pick_bn(m, n);
+  CUtensorMap tx, tw;
+  if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
+  if (int rc = make_tmap_bf16_2d(&tw, w, n, k, ldw, bn)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define NVLLM_GEMM_CASE(BNV)                                                                     \
+  case BNV:                                                                                      \
+    return out_dtype == NVLLM_BF16 ? launch_gemm<BNV, bf16>(tx, tw, y, m, n, k, ldy, st)         \
+                                   : launch_gemm<BNV, float>(tx, tw, y, m, n, k, ldy, st)
+  switch (bn) {
+    NVLLM_GEMM_CASE(256);
+    NVLLM_GEMM_CASE(128);
+    NVLLM_GEMM_CASE(64);
+    default:
+      NVLLM_GEMM_CASE(32);
+  }
+#undef NVLLM_GEMM_CASE
+}

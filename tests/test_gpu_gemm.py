@@ -1,0 +1,83 @@
+"""-m gpu parity tests for the tcgen05 GEMM (K5) through the C ABI: against the numpy oracle (linear.rs contract
+y = x . W^T, bf16 in, f32 accumulate) at sizes the oracle finishes in seconds, and against the on-device
+CUDA-core check kernel at the full Qwen3 shapes."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import layers as O
+from tests.util import assert_close, randn_bf16, to_dev_bf16, to_np_f32
+
+pytestmark = pytest.mark.gpu
+
+# f32 accumulation in a different order than numpy + one bf16 rounding of the output: 1 bf16 ulp (2^-8) + abs slack
+ATOL, RTOL = 2e-2, 2 ** -7
+
+SHAPES = [
+    (128, 128, 64), (1, 8, 64), (5, 40, 128), (129, 136, 192), (256, 4096, 1024), (300, 1024, 2048),
+    (256, 6144, 1024), (64, 1024, 3072), (7, 264, 4096), (512, 512, 512),
+]
+
+
+@pytest.mark.parametrize("m,n,k", SHAPES)
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_gemm_vs_oracle(cuda, m, n, k, out_dtype):
+    from nano_vllm_rs_b200 import ops
+    rng = np.random.default_rng(m * 31 + n * 7 + k)
+    x = randn_bf16(rng, (m, k)); w = randn_bf16(rng, (n, k), 0.05)
+    y = ops.gemm_bf16(to_dev_bf16(x, cuda), to_dev_bf16(w, cuda), out_dtype=out_dtype)
+    torch.cuda.synchronize()
+    ref = O.linear(x, w, out_bf16=(out_dtype == torch.bfloat16))
+    assert_close(to_np_f32(y), ref, ATOL if out_dtype == torch.bfloat16 else 2e-3, RTOL if out_dtype == torch.bfloat16 else 1e-4, f"gemm {m}x{n}x{k}")
+
+
+@pytest.mark.parametrize("bn", ["32", "64", "128", "256"])
+def test_gemm_every_tile_width(cuda, bn, monkeypatch):
+    """Force each BLOCK_N instantiation (the heuristic would otherwise hide some) in a fresh process."""
+    import subprocess, sys, os
+    code = (
+        "import numpy as np, torch, sys; sys.path.insert(0, '.');"
+        "from nano_vllm_rs_b200 import ops;"
+        "g=torch.Generator(device='cuda').manual_seed(1);"
+        "x=torch.randn((300,1024),generator=g,device='cuda').to(torch.bfloat16);"
+        "w=(torch.randn((1160,1024),generator=g,device='cuda')*0.05).to(torch.bfloat16);"
+        "y=ops.gemm_bf16(x,w,out_dtype=torch.float32); r=ops.gemm_bf16(x,w,out_dtype=torch.float32,simt=True);"
+        "torch.cuda.synchronize(); d=(y-r).abs().max().item(); print('maxdiff',d); assert d<2e-3, d"
+    )
+    env = dict(os.environ, NVLLM_GEMM_BN=bn)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 151936, 1024), (2048, 6144, 1024), (512, 24576, 4096), (512, 4096, 12288), (4096, 4096, 4096)])
+def test_gemm_full_size_vs_device_check(cuda, m, n, k):
+    """Full Qwen3 shapes (lm_head, prefill qkv, 8B gate_up / down): tcgen05 vs the CUDA-core check kernel (both
+    accumulate in f32; only the summation order differs)."""
+    from nano_vllm_rs_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(m + n + k)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn((n, k), generator=g, device=cuda) * 0.02).to(torch.bfloat16)
+    y = ops.gemm_bf16(x, w, out_dtype=torch.float32)
+    r = ops.gemm_bf16(x, w, out_dtype=torch.float32, simt=True)
+    torch.cuda.synchronize()
+    assert_close(to_np_f32(y), to_np_f32(r), 3e-3, 1e-4, f"gemm full {m}x{n}x{k}")
+    # linearity (size-independent property): (2x) . W^T == 2 (x . W^T) exactly in f32 (power-of-two scale)
+    y2 = ops.gemm_bf16((x.float() * 2).to(torch.bfloat16), w, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    assert torch.equal(y2, y * 2)
+
+
+def test_gemm_strided_views(cuda):
+    """Leading dimensions larger than the logical width (column slices of packed buffers, as o_proj reading the
+    attention output or TP shards of a full weight)."""
+    from nano_vllm_rs_b200 import ops
+    rng = np.random.default_rng(3)
+    xb = randn_bf16(rng, (70, 512)); wb = randn_bf16(rng, (200, 512), 0.05)
+    xd, wd = to_dev_bf16(xb, cuda), to_dev_bf16(wb, cuda)
+    out = torch.zeros((70, 400), dtype=torch.bfloat16, device=cuda)
+    ops.gemm_bf16(xd[:, 128:384], wd[:, 256:512], out=out[:, 200:400])
+    torch.cuda.synchronize()
+    ref = O.linear(xb[:, 128:384], wb[:, 256:512])
+    assert_close(to_np_f32(out[:, 200:400]), ref, ATOL, RTOL, "strided gemm")
+    assert float(out[:, :200].abs().max()) == 0.0
