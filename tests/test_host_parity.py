@@ -1,0 +1,142 @@
+"""CPU tests (no GPU): the C++ host layer behind include/nvllm_engine.h against the Python oracle, BIT-EXACT —
+XXH64 digests, block ids / ref-counts / hashes, free-list order, block tables, slot mappings, context lengths,
+cu_seqlens, prefill/decode order and preemption — every step of randomised and Appendix-B workloads."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from nano_vllm_rs_b200 import engine as E
+from oracle import host as H
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = json.load(open(os.path.join(ROOT, "tests", "golden", "xxh64.json")))
+
+
+def test_compute_hash_golden_vectors_through_c_abi():
+    for v in GOLD["compute_hash"]:
+        prefix = int(v["prefix"], 16) if isinstance(v["prefix"], str) else v["prefix"]
+        assert E.compute_hash(v["tokens"], prefix) == int(v["digest"], 16)
+    rng = np.random.default_rng(0)
+    for n in [1, 2, 3, 4, 5, 7, 16, 255, 256, 257, 1024]:
+        t = rng.integers(-5, 151936, n)
+        assert E.compute_hash(t) == H.compute_hash(t.tolist())
+        assert E.compute_hash(t, 2 ** 64 - 3) == H.compute_hash(t.tolist(), 2 ** 64 - 3)
+
+
+def _eq(a, b, what):
+    if a is None or b is None:
+        assert a is None and b is None, what
+        return
+    assert a.dtype == b.dtype, (what, a.dtype, b.dtype)
+    assert np.array_equal(a, b), (what, a, b)
+
+
+def lockstep(prompts, bs, num_blocks, max_tokens, max_batched, max_seqs, eos=None, seed=0, check_blocks=True):
+    """Drive the C++ scheduler and the oracle with the same token stream; compare everything at every step."""
+    ocfg = H.Config(kvcache_block_size=bs, num_kvcache_blocks=num_blocks, max_num_batched_tokens=max_batched,
+                    max_num_seqs=max_seqs, eos_token_id=eos)
+    osc = H.Scheduler(ocfg)
+    ccfg = E.Config("tiny", kvcache_block_size=bs, num_kvcache_blocks=num_blocks, max_num_batched_tokens=max_batched,
+                    max_num_seqs=max_seqs, eos_token_id=eos)
+    csc = E.Scheduler(ccfg)
+    oseqs = []
+    for p, mt in zip(prompts, max_tokens):
+        s = H.Sequence(p, H.SamplingParams(temperature=0.0, max_tokens=mt), block_size=bs)
+        oseqs.append(s)
+        osc.add_sequence(s)
+        cid = csc.add_sequence(p, E.SamplingParams(temperature=0.0, max_tokens=mt))
+        assert cid == len(oseqs) - 1
+    id0 = oseqs[0].seq_id
+    rng = np.random.default_rng(seed)
+    steps = 0
+    while not osc.is_finished():
+        assert not csc.is_finished()
+        batch, is_prefill = osc.schedule()
+        o = H.prepare_prefill(batch, bs) if is_prefill else H.prepare_decode(batch, bs)
+        c = csc.schedule()
+        assert c.is_prefill == is_prefill, steps
+        _eq(c.seq_ids, np.asarray([s.seq_id - id0 for s in batch], np.int64), "seq_ids")
+        _eq(c.input_ids, o.input_ids, "input_ids"); _eq(c.positions, o.positions, "positions")
+        _eq(c.slot_mapping, o.slot_mapping, "slot_mapping")
+        _eq(c.cu_seqlens_q, o.cu_seqlens_q, "cu_q"); _eq(c.cu_seqlens_k, o.cu_seqlens_k, "cu_k")
+        _eq(c.context_lens, o.context_lens, "context_lens"); _eq(c.block_tables, o.block_tables, "block_tables")
+        if is_prefill:
+            assert (c.max_seqlen_q, c.max_seqlen_k) == (o.max_seqlen_q, o.max_seqlen_k)
+        if check_blocks:
+            assert csc.free_list() == list(osc.block_manager.free_block_ids), steps
+            for b in osc.block_manager.blocks:
+                assert csc.block_info(b.block_id) == (b.ref_count, b.hash), (steps, b.block_id)
+        toks = rng.integers(0, 50, len(batch)).tolist()   # small vocab: EOS and prefix collisions do happen
+        osc.postprocess(batch, toks)
+        csc.postprocess(toks)
+        st = csc.get_stats()
+        assert (st["waiting"], st["running"], st["finished"], st["preemptions"]) == (
+            len(osc.waiting), len(osc.running), osc.num_finished, osc.num_preemptions), steps
+        assert st["cached_blocks"] == len(osc.block_manager.hash_to_block_id)
+        steps += 1
+        assert steps < 100000
+    assert csc.is_finished()
+    for i, s in enumerate(oseqs):
+        cs = csc.sequence(i)
+        assert cs["token_ids"] == s.token_ids and cs["status"] == s.status and cs["num_prompt_tokens"] == s.num_prompt_tokens
+    return steps
+
+
+def test_reference_block_manager_cases_bs4():
+    # block_manager.rs:426-506 scenarios, in lockstep
+    lockstep([[1, 2, 3, 4, 5, 6, 7, 8, 9]], 4, 10, [3], 1000, 10)
+    lockstep([[1, 2, 3, 4, 5, 6, 7, 8], [1, 2, 3, 4, 9, 10, 11, 12]], 4, 10, [2, 2], 1000, 10)
+    lockstep([[1, 2, 3]], 4, 10, [6], 1000, 10)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_workloads_with_shared_prefixes_eos_and_preemption(seed):
+    rng = np.random.default_rng(seed)
+    bs = [4, 16, 16, 32, 4, 16][seed]
+    n = int(rng.integers(3, 20))
+    shared = rng.integers(0, 50, int(rng.integers(0, 5)) * bs).tolist()
+    prompts = []
+    for _ in range(n):
+        own = rng.integers(0, 50, int(rng.integers(1, 4 * bs))).tolist()
+        prompts.append((shared + own) if rng.random() < 0.6 else own)
+    need = max((len(p) + 40 + bs - 1) // bs for p in prompts)
+    num_blocks = int(need + rng.integers(0, 2 * need))          # tight: forces preemption and recompute
+    max_tokens = [int(rng.integers(1, 40)) for _ in prompts]
+    steps = lockstep(prompts, bs, num_blocks, max_tokens, max_batched=int(rng.integers(8 * bs, 40 * bs)),
+                     max_seqs=int(rng.integers(2, 12)), eos=7 if seed % 2 else None, seed=seed)
+    assert steps > 0
+
+
+def test_cfg1_trace_in_lockstep():
+    rng = np.random.default_rng(1234)
+    prompts = [rng.integers(0, 151936, 128).tolist() for _ in range(4)]
+    assert lockstep(prompts, 256, 1000, [65] * 4, 32768, 512) == 65
+
+
+def test_cfg2_trace_scaled_in_lockstep():
+    rng = np.random.default_rng(1234)
+    prompts = [rng.integers(0, 151936, 512).tolist() for _ in range(8)]
+    assert lockstep(prompts, 256, 32, [512] * 8, 1024, 512, check_blocks=False) == 4 + 511
+
+
+def test_cfg4_shared_prefix_scaled_in_lockstep():
+    rng = np.random.default_rng(4321)
+    prefix = rng.integers(0, 151936, 64).tolist()
+    prompts = [prefix + rng.integers(0, 151936, 16).tolist() for _ in range(6)]
+    lockstep(prompts, 16, 64, [3] * 6, 200, 512)
+
+
+def test_config_defaults_and_validate():
+    c = E.Config("qwen3-0.6b")
+    assert (c.max_num_batched_tokens, c.max_num_seqs, c.max_model_len, c.kvcache_block_size) == (32768, 512, 4096, 256)
+    assert (c.hidden_size, c.num_hidden_layers, c.num_attention_heads, c.num_key_value_heads, c.head_dim) == (1024, 28, 16, 8, 128)
+    c.validate()
+    r = E.Config("reference-default")      # qwen3.rs:70-89
+    assert (r.hidden_size, r.intermediate_size, r.num_hidden_layers, r.num_key_value_heads, r.qk_norm) == (4096, 11008, 32, 32, 0)
+    with pytest.raises(Exception):
+        E.Config("qwen3-8b", tensor_parallel_size=9).validate()     # config.rs:99-101
+    with pytest.raises(Exception):
+        E.Config("qwen3-8b", tensor_parallel_size=3).validate()     # qwen3.rs:111-113
+    E.Config("qwen3-32b", tensor_parallel_size=8, tp_rank=7, max_model_len=32768 + 64).validate()
