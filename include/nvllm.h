@@ -102,11 +102,13 @@ int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache, 
  * keys 0 .. Lk-Lq+j), which is the plain causal mask when Lq == Lk.
  * If block_tables == NULL keys/values come from the dense k, v: [total_k, Hkv, D];
  * otherwise (prefix-cache prefill) they are read from the paged cache through block_tables[i,:]
- * (the new K/V of this step must already have been stored — note N2 in SURVEY.md §8). */
+ * (the new K/V of this step must already have been stored — note N2 in SURVEY.md §8).
+ * total_q / total_k: rows of q / of the dense k, v (bounds of the TMA descriptors; total_k is ignored when paged).
+ * Requires Lk >= Lq per sequence and head_dim == 128; runs on tcgen05 tensor cores. */
 int nvllm_varlen_prefill_attention(void* out, const void* q, const void* k, const void* v,
                                    const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                                   int32_t batch, int32_t max_seqlen_q, int32_t max_seqlen_k,
-                                   int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                                   int32_t batch, int32_t total_q, int32_t total_k,
+                                   int32_t max_seqlen_q, int32_t max_seqlen_k, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
                                    int64_t q_token_stride, int64_t kv_token_stride,
                                    int64_t out_token_stride, const void* k_cache,
                                    const void* v_cache, const int32_t* block_tables,

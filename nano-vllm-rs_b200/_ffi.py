@@ -42,7 +42,7 @@ PROTOTYPES = {
     "nvllm_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "nvllm_paged_decode_choose_splits": (i32, [i32, i32, i32, i32]),
     "nvllm_paged_decode_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64, LP, f32, vp, sz, i32, i32, vp]),
-    "nvllm_varlen_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64,
+    "nvllm_varlen_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64,
                                              vp, vp, vp, i32, LP, f32, i32, vp]),
     "nvllm_gemm_workspace_bytes": (sz, [i32, i32, i32]),
     "nvllm_gemm_bf16": (i32, [vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, vp, sz, vp]),

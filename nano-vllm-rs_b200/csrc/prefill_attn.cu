@@ -1,0 +1,342 @@
+// prefill_attn.cu — K3 / K4: varlen causal flash-attention forward on tcgen05 / TMEM (tensor-bound).
+//
+// Replaces Attention::flash_attention_varlen + create_causal_mask (reference src/layers/attention.rs:177-208,
+// 321-339: per-sequence loop, O(L^2) host-built mask, dense matmul) and flash_attention_varlen_with_cache
+// (:211-222, prefill of the uncached suffix against the paged prefix).
+//
+// One CTA = 256 query rows of one (sequence, head): two "row groups" (RG) of 128 threads, one query row per
+// thread, sharing the K/V tiles of the KV head.  While one RG runs its softmax on CUDA cores the tensor core
+// executes the other RG's MMAs (ping-pong).
+//   warp 8 (one lane)   TMA producer: Q once (2 x 128 x 128), then K/V tiles of 64 keys through a STAGES ring;
+//                       dense K/V via a 2-D map, paged K/V via a 4-D map (d, token, head, block) + block_tables
+//   RG thread 0         MMA issuer:  S[128x64]  = Q[128x128] . K^T   (8 x tcgen05.mma M128 N64 K16, both K-major)
+//                                    Oj[128x128] = P[128x64] . V      (4 x tcgen05.mma M128 N128 K16, V MN-major)
+//   RG threads          S: tcgen05.ld -> online softmax in registers (row-local: no shuffles) -> P as bf16 into
+//                       shared memory in the SWIZZLE_128B K-major layout;  Oj: tcgen05.ld -> acc = acc*corr + Oj
+// TMEM: 512 columns = 2 RG x (S 64 + Oj 128, padded to 256).  Causal mask is bottom-right aligned
+// (row r of Lq sees keys <= Lk - Lq + r) so the same kernel serves Lq == Lk and suffix-over-prefix.
+#include "tc.cuh"
+
+namespace nvllm {
+
+int check_layout(const nvllm_kv_layout* L);  // store_kvcache.cu
+
+namespace pf {
+constexpr int D = 128, BM = 128, BN = 64, STAGES = 3;
+constexpr int kQBytes = BM * D * 2;          // one RG's Q tile: 2 halves of [128 x 64]
+constexpr int kKVBytes = BN * D * 2;         // one K (or V) tile: 2 halves of [64 x 64]
+constexpr int kPBytes = BM * BN * 2;         // one RG's P tile [128 x 64]
+constexpr int kSmemQ = 0;
+constexpr int kSmemK = kSmemQ + 2 * kQBytes;
+constexpr int kSmemV = kSmemK + STAGES * kKVBytes;
+constexpr int kSmemP = kSmemV + STAGES * kKVBytes;
+constexpr int kSmemBar = kSmemP + 2 * kPBytes;
+constexpr int kNumBars = 1 + 2 * STAGES + 4;
+constexpr int kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;
+constexpr int kThreads = 288;
+}  // namespace pf
+
+struct PrefillParams {
+  bf16* out;
+  const int32_t* cu_q;
+  const int32_t* cu_k;
+  const int32_t* tables;  // NULL: dense K/V
+  int H, Hkv, max_blocks, block_size, box_tok;
+  int64_t out_stride;
+  float scale_log2;
+};
+
+__global__ void __launch_bounds__(pf::kThreads, 1)
+prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+                    const __grid_constant__ CUtensorMap tmap_v, const PrefillParams p) {
+  using namespace pf;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bars = smem_base + kSmemBar;
+  const uint32_t q_full = bars;
+  auto kv_full = [&](int s) { return bars + (1 + s) * 8; };
+  auto kv_empty = [&](int s) { return bars + (1 + STAGES + s) * 8; };
+  auto s_full = [&](int g) { return bars + (1 + 2 * STAGES + g) * 8; };
+  auto o_full = [&](int g) { return bars + (1 + 2 * STAGES + 2 + g) * 8; };
+  const uint32_t tmem_slot = bars + kNumBars * 8;
+
+  const int seq = blockIdx.z, head = blockIdx.y, qblk = blockIdx.x;
+  const int kvh = head / (p.H / p.Hkv);
+  const int q0 = __ldg(p.cu_q + seq), Lq = __ldg(p.cu_q + seq + 1) - q0;
+  const int k0 = __ldg(p.cu_k + seq), Lk = __ldg(p.cu_k + seq + 1) - k0;
+  if (qblk * 2 * BM >= Lq) return;  // uniform per CTA: nothing allocated yet
+  const int shift = Lk - Lq;        // bottom-right alignment
+  // number of KV tiles each row group needs (0 when the group has no valid row)
+  auto tiles_for = [&](int g) {
+    const int first = qblk * 2 * BM + g * BM;
+    if (first >= Lq) return 0;
+    const int last = min(first + BM, Lq) - 1;
+    const int visible = max(1, min(Lk, shift + last + 1));  // keys the group's last row sees
+    return (visible + BN - 1) / BN;
+  };
+  const int n_rg[2] = {tiles_for(0), tiles_for(1)};
+  const int n_cta = max(n_rg[0], n_rg[1]);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k); tma_prefetch_desc(&tmap_v);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < STAGES; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 2); }
+    for (int g = 0; g < 2; ++g) { mbar_init(s_full(g), 1); mbar_init(o_full(g), 1); }
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<uint32_t*>(smem_gen + kSmemBar + kNumBars * 8);
+
+  if (warp == 8) {
+    if (lane == 0) {
+      // ===== TMA producer =====
+      mbar_expect_tx(q_full, 2 * kQBytes);
+      for (int g = 0; g < 2; ++g)
+        for (int hf = 0; hf < 2; ++hf)
+          tma_load_2d(smem_base + kSmemQ + g * kQBytes + hf * (BM * 128), &tmap_q, q_full, head * D + hf * 64,
+                      q0 + qblk * 2 * BM + g * BM);
+      const int32_t* table = p.tables ? p.tables + static_cast<int64_t>(seq) * p.max_blocks : nullptr;
+      for (int j = 0; j < n_cta; ++j) {
+        const int st = j % STAGES;
+        mbar_wait(kv_empty(st), ((j / STAGES) & 1) ^ 1);
+        mbar_expect_tx(kv_full(st), 2 * kKVBytes);
+        const uint32_t dk = smem_base + kSmemK + st * kKVBytes, dv = smem_base + kSmemV + st * kKVBytes;
+        if (table == nullptr) {
+          for (int hf = 0; hf < 2; ++hf) {
+            tma_load_2d(dk + hf * (BN * 128), &tmap_k, kv_full(st), kvh * D + hf * 64, k0 + j * BN);
+            tma_load_2d(dv + hf * (BN * 128), &tmap_v, kv_full(st), kvh * D + hf * 64, k0 + j * BN);
+          }
+        } else {
+          for (int c = 0; c < BN / p.box_tok; ++c) {  // box_tok = min(64, block_size) tokens per TMA box
+            const int tok = j * BN + c * p.box_tok;
+            const int bi = tok / p.block_size;
+            int blk = bi < p.max_blocks ? __ldg(table + bi) : -1;
+            // a block id < 0 (only past the sequence end) is redirected far out of bounds: TMA zero-fills
+            const int blk_c = blk < 0 ? 0x3fffff : blk;
+            for (int hf = 0; hf < 2; ++hf) {
+              const uint32_t off = hf * (BN * 128) + c * p.box_tok * 128;
+              tma_load_4d(dk + off, &tmap_k, kv_full(st), hf * 64, tok - bi * p.block_size, kvh, blk_c);
+              tma_load_4d(dv + off, &tmap_v, kv_full(st), hf * 64, tok - bi * p.block_size, kvh, blk_c);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ===== row groups: MMA issue (thread 0 of the group) + softmax + output =====
+    const int g = warp >> 2;               // row group 0 / 1
+    const int t = threadIdx.x & 127;       // row within the group's tile == TMEM lane
+    const int n_my = n_rg[g];
+    const bool issuer = t == 0;
+    const int row = qblk * 2 * BM + g * BM + t;  // row within the sequence's queries
+    const int limit = shift + row;               // last visible key index
+    const uint32_t tS = tmem_base + g * 256 + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    const uint32_t tO = tS + 128;
+    const uint32_t tS_mma = tmem_base + g * 256, tO_mma = tS_mma + 128;
+    const uint32_t sQ = smem_base + kSmemQ + g * kQBytes;
+    const uint32_t sP = smem_base + kSmemP + g * kPBytes;
+    uint8_t* sP_gen = smem_gen + kSmemP + g * kPBytes;
+    constexpr uint32_t idesc_s = umma_idesc_bf16(BM, BN, 0, 0);   // Q K-major, K K-major
+    constexpr uint32_t idesc_o = umma_idesc_bf16(BM, D, 0, 1);    // P K-major, V MN-major
+
+    auto issue_s = [&](int j) {  // S = Q . K_j^T
+      const int st = j % STAGES;
+      mbar_wait(kv_full(st), (j / STAGES) & 1);
+      tc_fence_after();
+      const uint32_t sK = smem_base + kSmemK + st * kKVBytes;
+#pragma unroll
+      for (int ks = 0; ks < D / 16; ++ks) {
+        const uint64_t ad = umma_desc_sw128(sQ + (ks >> 2) * (BM * 128) + (ks & 3) * 32, 16, 1024);
+        const uint64_t bd = umma_desc_sw128(sK + (ks >> 2) * (BN * 128) + (ks & 3) * 32, 16, 1024);
+        umma_bf16_ss(tS_mma, ad, bd, idesc_s, ks != 0);
+      }
+      umma_commit(s_full(g));
+    };
+
+    float m_run = -INFINITY, l_run = 0.f;
+    float acc[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) acc[d] = 0.f;
+
+    if (issuer && n_my > 0) {
+      mbar_wait(q_full, 0);
+      issue_s(0);
+    }
+    for (int j = 0; j < n_my; ++j) {
+      const int st = j % STAGES;
+      // ---- softmax on S_j ---------------------------------------------------------------------
+      mbar_wait(s_full(g), j & 1);
+      tc_fence_after();
+      uint32_t sr[2][32];
+      tmem_ld_32x32b_x32(tS, sr[0]);
+      tmem_ld_32x32b_x32(tS + 32, sr[1]);
+      tmem_ld_wait();
+      const int kbase = j * BN;
+      const bool need_mask = (kbase + BN - 1 > limit) || (kbase + BN > Lk);
+      float mx = m_run;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        float s = __uint_as_float(sr[c >> 5][c & 31]);
+        if (need_mask && (kbase + c > limit || kbase + c >= Lk)) s = -INFINITY;
+        sr[c >> 5][c & 31] = __float_as_uint(s);
+        mx = fmaxf(mx, s);
+      }
+      const float m_safe = (mx == -INFINITY) ? 0.f : mx;
+      const float corr = fast_exp2((m_run - m_safe) * p.scale_log2);
+      const float moff = m_safe * p.scale_log2;
+      float lsum = 0.f;
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) {  // 8 chunks of 8 keys = 16 bytes of bf16 P each
+        uint32_t pk[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = c8 * 8 + e * 2;
+          const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff));
+          lsum += p0 + p1;
+          pk[e] = pack_bf16x2(p0, p1);
+        }
+        // SWIZZLE_128B K-major: row t at t*128 bytes, 16-byte chunk index XOR (row & 7)
+        *reinterpret_cast<uint4*>(sP_gen + t * 128 + ((c8 ^ (t & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      }
+      l_run = l_run * corr + lsum;
+      m_run = mx;
+      tc_fence_before();
+      fence_proxy_async();  // generic-proxy writes of P -> visible to the tensor core (async proxy)
+      asm volatile("bar.sync %0, 128;\n" ::"r"(1 + g) : "memory");
+      // ---- O_j = P . V_j, then S_{j+1} ----------------------------------------------------------
+      if (issuer) {
+        tc_fence_after();
+        const uint32_t sV = smem_base + kSmemV + st * kKVBytes;
+#pragma unroll
+        for (int ks = 0; ks < BN / 16; ++ks) {
+          const uint64_t ad = umma_desc_sw128(sP + ks * 32, 16, 1024);
+          // V tile: rows = keys (k), 64 contiguous d per row; 2 MN groups (d halves) 8 KiB apart, 8 keys per 1 KiB
+          const uint64_t bd = umma_desc_sw128(sV + ks * 2048, BN * 128, 1024);
+          umma_bf16_ss(tO_mma, ad, bd, idesc_o, ks != 0);
+        }
+        umma_commit(o_full(g));
+        umma_commit(kv_empty(st));
+        if (j + 1 < n_my) issue_s(j + 1);
+      }
+      // ---- acc = acc * corr + O_j ------------------------------------------------------------------
+      mbar_wait(o_full(g), j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t orr[32];
+        tmem_ld_32x32b_x32(tO + c * 32, orr);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) acc[c * 32 + e] = fmaf(acc[c * 32 + e], corr, __uint_as_float(orr[e]));
+      }
+      tc_fence_before();
+    }
+    // tiles this group does not need still have to be released for the other group / the producer
+    if (issuer) {
+      for (int j = n_my; j < n_cta; ++j) {
+        const int st = j % STAGES;
+        mbar_wait(kv_full(st), (j / STAGES) & 1);
+        mbar_arrive(kv_empty(st));
+      }
+    }
+    // ---- output -------------------------------------------------------------------------------------
+    if (n_my > 0 && row < Lq) {
+      const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+      bf16* orow = p.out + static_cast<int64_t>(q0 + row) * p.out_stride + head * D;
+#pragma unroll
+      for (int c = 0; c < D / 8; ++c) {
+        uint4 v;
+        v.x = pack_bf16x2(acc[c * 8 + 0] * inv, acc[c * 8 + 1] * inv);
+        v.y = pack_bf16x2(acc[c * 8 + 2] * inv, acc[c * 8 + 3] * inv);
+        v.z = pack_bf16x2(acc[c * 8 + 4] * inv, acc[c * 8 + 5] * inv);
+        v.w = pack_bf16x2(acc[c * 8 + 6] * inv, acc[c * 8 + 7] * inv);
+        *reinterpret_cast<uint4*>(orow + c * 8) = v;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+}  // namespace nvllm
+
+extern "C" int nvllm_varlen_prefill_attention(void* out, const void* q, const void* k, const void* v,
+                                              const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                                              int32_t batch, int32_t total_q, int32_t total_k,
+                                              int32_t max_seqlen_q, int32_t max_seqlen_k, int32_t num_heads,
+                                              int32_t num_kv_heads, int32_t head_dim, int64_t q_token_stride,
+                                              int64_t kv_token_stride, int64_t out_token_stride,
+                                              const void* k_cache, const void* v_cache,
+                                              const int32_t* block_tables, int32_t max_blocks_per_seq,
+                                              const nvllm_kv_layout* layout, float scale, int32_t dtype,
+                                              void* stream) {
+  using namespace nvllm;
+  NVLLM_CHECK_ARG(dtype == NVLLM_BF16, NVLLM_ERR_DTYPE, "prefill_attention: dtype %d (bf16 only)", dtype);
+  NVLLM_CHECK_ARG(head_dim == pf::D, NVLLM_ERR_ARG, "prefill_attention: head_dim %d (128 only)", head_dim);
+  NVLLM_CHECK_ARG(batch >= 0 && batch <= 65535 && total_q >= 0 && max_seqlen_q >= 0, NVLLM_ERR_ARG,
+                  "prefill_attention: batch %d total_q %d", batch, total_q);
+  if (batch == 0 || total_q == 0 || max_seqlen_q == 0) return 0;
+  NVLLM_CHECK_ARG(num_heads > 0 && num_kv_heads > 0 && num_heads % num_kv_heads == 0 && num_heads <= 65535,
+                  NVLLM_ERR_ARG, "prefill_attention: heads %d / kv heads %d", num_heads, num_kv_heads);
+  NVLLM_CHECK_ARG(out && q && cu_seqlens_q && cu_seqlens_k, NVLLM_ERR_ARG, "prefill_attention: NULL pointer");
+  NVLLM_CHECK_ARG(aligned16(out) && out_token_stride % 8 == 0 && out_token_stride >= (int64_t)num_heads * head_dim,
+                  NVLLM_ERR_ALIGN, "prefill_attention: out alignment / stride");
+  const bool paged = block_tables != nullptr;
+  CUtensorMap tq, tk, tv;
+  if (int rc = make_tmap_bf16_2d(&tq, q, total_q, (int64_t)num_heads * head_dim, q_token_stride, pf::BM)) return rc;
+  PrefillParams p;
+  p.box_tok = pf::BN;
+  if (!paged) {
+    NVLLM_CHECK_ARG(k && v && total_k > 0, NVLLM_ERR_ARG, "prefill_attention: dense k/v missing");
+    if (int rc = make_tmap_bf16_2d(&tk, k, total_k, (int64_t)num_kv_heads * head_dim, kv_token_stride, pf::BN)) return rc;
+    if (int rc = make_tmap_bf16_2d(&tv, v, total_k, (int64_t)num_kv_heads * head_dim, kv_token_stride, pf::BN)) return rc;
+    p.block_size = 1;
+    p.max_blocks = 0;
+  } else {
+    if (int rc = check_layout(layout)) return rc;
+    NVLLM_CHECK_ARG(k_cache && v_cache && max_blocks_per_seq > 0, NVLLM_ERR_ARG, "prefill_attention: paged cache missing");
+    NVLLM_CHECK_ARG(layout->num_kv_heads == num_kv_heads && layout->head_dim == head_dim, NVLLM_ERR_ARG,
+                    "prefill_attention: layout heads/dim mismatch");
+    const int bs = layout->block_size;
+    NVLLM_CHECK_ARG(bs % 16 == 0 && (bs >= pf::BN ? bs % pf::BN == 0 : pf::BN % bs == 0), NVLLM_ERR_ARG,
+                    "prefill_attention: block_size %d must divide or be a multiple of %d", bs, pf::BN);
+    p.box_tok = bs < pf::BN ? bs : pf::BN;
+    const uint64_t dims[4] = {(uint64_t)head_dim, (uint64_t)bs, (uint64_t)num_kv_heads, 0x3fffffull};
+    const uint64_t strides[3] = {(uint64_t)layout->token_stride * 2, (uint64_t)layout->head_stride * 2,
+                                 (uint64_t)layout->block_stride * 2};
+    const uint32_t box[4] = {64, (uint32_t)p.box_tok, 1, 1};
+    if (int rc = make_tmap_bf16_nd(&tk, k_cache, 4, dims, strides, box)) return rc;
+    if (int rc = make_tmap_bf16_nd(&tv, v_cache, 4, dims, strides, box)) return rc;
+    p.block_size = bs;
+    p.max_blocks = max_blocks_per_seq;
+  }
+  p.out = static_cast<bf16*>(out);
+  p.cu_q = cu_seqlens_q;
+  p.cu_k = cu_seqlens_k;
+  p.tables = block_tables;
+  p.H = num_heads;
+  p.Hkv = num_kv_heads;
+  p.out_stride = out_token_stride;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  static bool attr_set = false;
+  if (!attr_set) {
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    attr_set = true;
+  }
+  (void)max_seqlen_k;
+  dim3 grid((max_seqlen_q + 2 * pf::BM - 1) / (2 * pf::BM), num_heads, batch);
+  prefill_attn_kernel<<<grid, pf::kThreads, pf::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, p);
+  NVLLM_LAUNCH_CHECK("prefill_attn_kernel");
+  return 0;
+}

@@ -14,6 +14,8 @@ namespace nvllm {
 // box = box_rows x 64 columns (128 bytes), SWIZZLE_128B, out-of-bounds elements read as zero.
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld,
                       int box_rows, int box_cols = 64);  // tc_host.cu
+int make_tmap_bf16_nd(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box);  // tc_host.cu
 
 #ifdef __CUDACC__
 

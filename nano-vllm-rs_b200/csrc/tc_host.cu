@@ -45,4 +45,25 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* base, int64_t rows, int64_t 
   return 0;
 }
 
+// General rank-N (<= 5) bf16 map: dims/box innermost first, strides in BYTES for dims 1..rank-1.
+int make_tmap_bf16_nd(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn fn = encode_fn();
+  NVLLM_CHECK_ARG(fn != nullptr, NVLLM_ERR_STATE, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+  NVLLM_CHECK_ARG(rank >= 2 && rank <= 5 && aligned16(base), NVLLM_ERR_ALIGN, "TMA nd: rank %d / base alignment", rank);
+  cuuint64_t d[5], st[4];
+  cuuint32_t b[5], es[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) {
+    NVLLM_CHECK_ARG(strides_bytes[i] % 16 == 0, NVLLM_ERR_ALIGN, "TMA nd: stride %d = %llu bytes", i,
+                    (unsigned long long)strides_bytes[i]);
+    st[i] = strides_bytes[i];
+  }
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), d, st, b, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  NVLLM_CHECK_ARG(r == CUDA_SUCCESS, NVLLM_ERR_ARG, "cuTensorMapEncodeTiled (rank %d) failed (%d)", rank, (int)r);
+  return 0;
+}
+
 }  // namespace nvllm

@@ -77,7 +77,7 @@ def varlen_prefill_attention(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, 
     Hkv = layout.num_kv_heads if paged else k.shape[1]
     check(_ffi.lib().nvllm_varlen_prefill_attention(
         _p(out), _p(q), _p(k), _p(v), _p(cu_seqlens_q), _p(cu_seqlens_k), cu_seqlens_q.numel() - 1,
-        max_seqlen_q, max_seqlen_k, H, Hkv, D, q.stride(0), 0 if k is None else k.stride(0), out.stride(0),
+        N, 0 if k is None else k.shape[0], max_seqlen_q, max_seqlen_k, H, Hkv, D, q.stride(0), 0 if k is None else k.stride(0), out.stride(0),
         _p(k_cache), _p(v_cache), _p(block_tables), block_tables.shape[1] if paged else 0,
         layout if paged else None, scale, BF16, _stream()))
     return out
