@@ -243,3 +243,109 @@ class Scheduler:
         lib().nvllm_scheduler_sequence(self.h, seq_id, a.ctypes.data, n, None, None)
         return dict(token_ids=a[:n].tolist(), num_prompt_tokens=npt.value,
                     status=["Waiting", "Running", "Finished", "Preempted"][st.value])
+
+
+# ---------------------------------------------------------------------------- ModelRunner / LLMEngine
+
+
+class ModelRunner:
+    """ModelRunner (model_runner.rs:19-448) + Qwen3Model (qwen3.rs): C++ host runtime over the sm_100a kernels."""
+
+    def __init__(self, config: Config, comm=None, _handle=None):
+        self.config = config
+        self._owned = _handle is None
+        if _handle is None:
+            h = vp()
+            check(lib().nvllm_runner_create(C.byref(h), C.byref(config.c), comm))
+            _handle = h
+        self.h = _handle
+        self.vshard = config.vocab_size // config.tensor_parallel_size
+
+    def __del__(self):
+        if getattr(self, "_owned", False) and self.h:
+            lib().nvllm_runner_destroy(self.h)
+            self.h = None
+
+    def init_weights(self, seed=1234, std=0.02):
+        check(lib().nvllm_runner_init_weights(self.h, seed, std))
+
+    def load_weight(self, name, bf16_bits):
+        """bf16_bits: uint16 numpy array [rows, cols] (or [n] for norm weights) holding bf16 bit patterns."""
+        a = np.ascontiguousarray(bf16_bits, dtype=np.uint16)
+        rows, cols = (1, a.shape[0]) if a.ndim == 1 else a.shape
+        check(lib().nvllm_runner_load_weight(self.h, name.encode(), a.ctypes.data, rows, cols))
+
+    def execute_model(self, batch: Batch, return_logits=False):
+        """execute_model + sample_tokens (model_runner.rs:105-156): returns greedy token ids [num_seqs] (and logits)."""
+        n = batch.c.num_seqs
+        toks = np.zeros(n, np.int64)
+        logits = np.zeros((n, self.vshard), np.float32) if return_logits else None
+        check(lib().nvllm_runner_execute(self.h, C.byref(batch.c), toks.ctypes.data,
+                                         logits.ctypes.data if return_logits else None))
+        return (toks, logits) if return_logits else toks
+
+    def last_launches(self):
+        return lib().nvllm_runner_last_launches(self.h)
+
+    def time_decode_attention(self, iters=20):
+        ms, nbytes = f32(), i64()
+        check(lib().nvllm_runner_time_decode_attention(self.h, iters, C.byref(ms), C.byref(nbytes)))
+        return ms.value, nbytes.value
+
+
+class LLMEngine:
+    """LLMEngine (llm_engine.rs:23-362), synchronous: add_request / step / generate over token ids.
+    (Tokeniser, async streaming and stats facade are out of scope for the hot path — SURVEY.md §8f #4.)"""
+
+    def __init__(self, config: Config, comm=None, seed=1234, std=0.02, init_weights=True):
+        config.validate()
+        self.config = config
+        h = vp()
+        check(lib().nvllm_engine_create(C.byref(h), C.byref(config.c), comm))
+        self.h = h
+        self.scheduler = Scheduler(config, _handle=vp(lib().nvllm_engine_scheduler(h)))
+        self.model_runner = ModelRunner(config, _handle=vp(lib().nvllm_engine_runner(h)))
+        if init_weights:
+            self.model_runner.init_weights(seed, std)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().nvllm_engine_destroy(self.h)
+            self.h = None
+
+    def add_request(self, prompt_token_ids, sampling_params: SamplingParams = None) -> int:
+        return self.scheduler.add_sequence(prompt_token_ids, sampling_params)
+
+    def step(self):
+        """LLMEngine::step (llm_engine.rs:155-197). Returns (is_prefill, num_seqs, num_tokens)."""
+        p, s, t = i32(), i32(), i32()
+        check(lib().nvllm_engine_step(self.h, C.byref(p), C.byref(s), C.byref(t)))
+        return bool(p.value), s.value, t.value
+
+    def is_finished(self):
+        return bool(lib().nvllm_engine_is_finished(self.h))
+
+    def generate(self, prompts: List[List[int]], sampling_params: SamplingParams = None):
+        """LLMEngine::generate (llm_engine.rs:71-98) over token-id prompts; returns completion token ids per prompt."""
+        ids = [self.add_request(p, sampling_params) for p in prompts]
+        while not self.is_finished():
+            self.step()
+        out = []
+        for i in ids:
+            s = self.scheduler.sequence(i)
+            out.append(s["token_ids"][s["num_prompt_tokens"]:])
+        return out
+
+
+class LLMEngineBuilder:
+    """LLMEngineBuilder (llm_engine.rs:419-483)."""
+
+    def __init__(self, arch="qwen3-0.6b"):
+        self._cfg = Config(arch)
+
+    def max_num_seqs(self, v): self._cfg._set("max_num_seqs", v); return self
+    def max_num_batched_tokens(self, v): self._cfg._set("max_num_batched_tokens", v); return self
+    def tensor_parallel_size(self, v): self._cfg._set("tensor_parallel_size", v); return self
+    def enforce_eager(self, v): self._cfg._set("enforce_eager", v); return self
+    def num_kvcache_blocks(self, v): self._cfg._set("num_kvcache_blocks", v); return self
+    def build(self, **kw): return LLMEngine(self._cfg, **kw)
