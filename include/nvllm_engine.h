@@ -134,6 +134,10 @@ int nvllm_runner_kv_cache(nvllm_runner* r, int32_t layer, void** k_cache, void**
  * events (for the roofline line of bench.py); returns the average milliseconds per launch. */
 int nvllm_runner_time_decode_attention(nvllm_runner* r, int32_t iters, float* ms_per_launch, int64_t* alg_bytes);
 
+/* Replays the last decode step `iters` times with its inputs already resident in HBM (graph launches only; no host
+ * scheduling, no copies) between two CUDA events on the runner's stream; writes the total milliseconds. */
+int nvllm_runner_replay_decode(nvllm_runner* r, int32_t iters, float* ms_total);
+
 /* LLMEngine (llm_engine.rs:23-362): scheduler + runner; step() = schedule -> execute_model -> sample_tokens ->
  * postprocess (llm_engine.rs:155-197).  The async/streaming/tokeniser facade is out of scope. */
 typedef struct nvllm_engine nvllm_engine;

@@ -553,6 +553,32 @@ int nvllm_runner_kv_cache(nvllm_runner* r, int32_t layer, void** k_cache, void**
   return 0;
 }
 
+// Replays the last decode step `iters` times with its metadata already resident in HBM (no host work, no copies):
+// the device-only cost of one step.  KV writes land in the same slots every time (idempotent).
+int nvllm_runner_replay_decode(nvllm_runner* r, int32_t iters, float* ms_total) {
+  NVLLM_CHECK_ARG(r && iters > 0 && ms_total, NVLLM_ERR_ARG, "replay_decode: arguments");
+  NVLLM_CHECK_ARG(r->last_decode_b > 0 && r->d_ctx != nullptr, NVLLM_ERR_STATE, "replay_decode: no decode step has run yet");
+  const int P = r->last_decode_b;
+  auto it = r->graphs.find(P);
+  const bool use_graph = !r->cfg.enforce_eager && it != r->graphs.end() && it->second.exec != nullptr;
+  nvllm_batch dummy;
+  memset(&dummy, 0, sizeof(dummy));
+  cudaEvent_t e0, e1;
+  NVLLM_CUDA(cudaEventCreate(&e0));
+  NVLLM_CUDA(cudaEventCreate(&e1));
+  NVLLM_CUDA(cudaEventRecord(e0, r->stream));
+  for (int i = 0; i < iters; ++i) {
+    if (use_graph) NVLLM_CUDA(cudaGraphLaunch(it->second.exec, r->stream));
+    else RUN(r->forward(P, P, false, false, dummy));
+  }
+  NVLLM_CUDA(cudaEventRecord(e1, r->stream));
+  NVLLM_CUDA(cudaEventSynchronize(e1));
+  NVLLM_CUDA(cudaEventElapsedTime(ms_total, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return 0;
+}
+
 // Re-launches the paged decode attention on the last decode batch's metadata (still resident), cycling through the
 // layers' caches so that consecutive launches never re-read the same KV from L2; CUDA events on the runner's stream.
 int nvllm_runner_time_decode_attention(nvllm_runner* r, int32_t iters, float* ms_per_launch, int64_t* alg_bytes) {

@@ -71,6 +71,7 @@ ENGINE_PROTOTYPES = {
     "nvllm_runner_last_launches": (i64, [vp]),
     "nvllm_runner_kv_cache": (i32, [vp, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(_ffi.KvLayout)]),
     "nvllm_runner_time_decode_attention": (i32, [vp, i32, C.POINTER(f32), C.POINTER(i64)]),
+    "nvllm_runner_replay_decode": (i32, [vp, i32, C.POINTER(f32)]),
     "nvllm_engine_create": (i32, [C.POINTER(vp), C.POINTER(CConfig), vp]),
     "nvllm_engine_destroy": (i32, [vp]),
     "nvllm_engine_scheduler": (vp, [vp]),
@@ -286,6 +287,12 @@ class ModelRunner:
 
     def last_launches(self):
         return lib().nvllm_runner_last_launches(self.h)
+
+    def replay_decode(self, iters):
+        """Device-only time (ms, CUDA events) of `iters` replays of the last decode step, inputs resident in HBM."""
+        ms = f32()
+        check(lib().nvllm_runner_replay_decode(self.h, iters, C.byref(ms)))
+        return ms.value
 
     def time_decode_attention(self, iters=20):
         ms, nbytes = f32(), i64()
