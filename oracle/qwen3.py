@@ -54,9 +54,39 @@ def seeded_weights(cfg, seed, std):
     return w
 
 
+def shard_weights(w, cfg, rank, tp):
+    """This rank's tensor-parallel slices, by the reference's sharding arithmetic: q/k/v/gate/up rows and o/down columns
+    divided by tp (qwen3.rs:157-159,273-292; linear.rs:154-172,202,249-267,303-307,401), LM head rows = vocab shard
+    (embed_head.rs:142-161), embedding and norms replicated.  Returns (sharded cfg, sharded weights)."""
+    H, Hkv, D, I, V = (cfg[k] for k in ("num_attention_heads", "num_key_value_heads", "head_dim", "intermediate_size", "vocab_size"))
+    assert H % tp == 0 and Hkv % tp == 0 and I % tp == 0 and V % tp == 0
+    c = dict(cfg, num_attention_heads=H // tp, num_key_value_heads=Hkv // tp, intermediate_size=I // tp)
+    rows = lambda a, n: a[rank * n:(rank + 1) * n]
+    cols = lambda a, n: a[:, rank * n:(rank + 1) * n]
+    out = {}
+    for name, a in w.items():
+        if name.endswith(("q_proj.weight",)):
+            out[name] = rows(a, H // tp * D)
+        elif name.endswith(("k_proj.weight", "v_proj.weight")):
+            out[name] = rows(a, Hkv // tp * D)
+        elif name.endswith(("gate_proj.weight", "up_proj.weight")):
+            out[name] = rows(a, I // tp)
+        elif name.endswith("o_proj.weight"):
+            out[name] = cols(a, H // tp * D)
+        elif name.endswith("down_proj.weight"):
+            out[name] = cols(a, I // tp)
+        else:
+            out[name] = a
+    head = w["model.embed_tokens.weight"] if cfg["tie_word_embeddings"] else w["lm_head.weight"]
+    out["__lm_head_shard__"] = rows(head, V // tp)
+    return c, out
+
+
 class Qwen3Oracle:
-    def __init__(self, cfg, weights, num_blocks, block_size):
+    def __init__(self, cfg, weights, num_blocks, block_size, allreduce=None):
+        """allreduce: callable(np.ndarray) -> sum over tensor-parallel ranks (the linear.rs:236 TODO); None = TP 1."""
         self.cfg, self.w, self.bs = cfg, weights, block_size
+        self.allreduce = allreduce
         Hkv, D = cfg["num_key_value_heads"], cfg["head_dim"]
         n = cfg["num_hidden_layers"]
         # create_kv_cache, model_runner.rs:364-396: per layer K and V zeros [num_blocks, block_size, Hkv, D]
@@ -96,12 +126,18 @@ class Qwen3Oracle:
             else:  # attention.rs:88-91
                 a = L.flash_attention_varlen(q, k, v, inp.cu_seqlens_q, inp.cu_seqlens_k, self.scale)
             o = L.linear(a.reshape(N, H * D), w[p + "self_attn.o_proj.weight"])  # qwen3.rs:236
+            if self.allreduce is not None:  # row-parallel partial sums, each a bf16 tensor (linear.rs:228-239)
+                o = L.round_bf16(self.allreduce(o))
             normed, h = L.add_rms_norm(o, h, w[p + "post_attention_layernorm.weight"], eps)  # :382-385
             wgu = np.concatenate([w[p + "mlp.gate_proj.weight"], w[p + "mlp.up_proj.weight"]], 0)  # linear.rs:421-433
             act = L.silu_and_mul(L.linear(normed, wgu))  # qwen3.rs:307-310
             mlp_out = L.linear(act, w[p + "mlp.down_proj.weight"])  # :312
+            if self.allreduce is not None:
+                mlp_out = L.round_bf16(self.allreduce(mlp_out))
         normed, h = L.add_rms_norm(mlp_out, h, w["model.norm.weight"], eps)  # qwen3.rs:389,501
         if inp.is_prefill:
             normed = L.extract_last_tokens(normed, inp.cu_seqlens_q)  # embed_head.rs:250-289
+        if "__lm_head_shard__" in w:  # vocab-sharded head: this rank's logits [num_seqs, vocab / tp]
+            return L.linear(normed, w["__lm_head_shard__"], out_bf16=False)
         head = w["model.embed_tokens.weight"] if c["tie_word_embeddings"] else w["lm_head.weight"]
         return L.linear(normed, head, out_bf16=False)  # embed_head.rs:292-306 (f32 logits for the sampler)
