@@ -1,0 +1,94 @@
+"""-m gpu, needs >= 2 GPUs (skipped otherwise): tensor-parallel engine (one process per GPU, NCCL all-reduce after
+o_proj / down_proj, vocab-sharded argmax) against the single-GPU engine on the same requests."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _tp_worker(rank, world, port, arch, prompts, max_tokens, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    try:
+        import torch.distributed as dist
+        from nano_vllm_rs_b200 import _ffi
+        from nano_vllm_rs_b200 import engine as E
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        lib = E.lib()
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            buf = (E.C.c_uint8 * 128)()
+            _ffi.check(lib.nvllm_comm_unique_id(buf))
+            uid.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        h = E.vp()
+        _ffi.check(lib.nvllm_comm_init(E.C.byref(h), bytes(uid.cpu().tolist()), rank, world))
+        cfg = E.Config(arch, kvcache_block_size=16, num_kvcache_blocks=64, tensor_parallel_size=world, tp_rank=rank)
+        sched, runner = E.Scheduler(cfg), E.ModelRunner(cfg, comm=h)
+        runner.init_weights(1234, 0.05)
+        for p in prompts:
+            sched.add_sequence(p, E.SamplingParams(temperature=0.0, max_tokens=max_tokens, ignore_eos=True))
+        trace = []
+        while not sched.is_finished():
+            b = sched.schedule()
+            toks, logits = runner.execute_model(b, return_logits=True)
+            trace.append((toks.copy(), logits.copy()))
+            sched.postprocess(toks)
+        q.put((rank, "ok", trace))
+        dist.barrier()
+        _ffi.check(lib.nvllm_comm_destroy(h))
+        dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        import traceback
+        q.put((rank, "fail: " + traceback.format_exc(), None))
+
+
+@pytest.mark.parametrize("world", [2])
+def test_tp_engine_matches_single_gpu(cuda, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    from nano_vllm_rs_b200 import engine as E
+    import torch.multiprocessing as mp
+    rng = np.random.default_rng(5)
+    prompts = [rng.integers(0, 1024, n).tolist() for n in (7, 40, 16, 33)]
+    max_tokens = 12
+    # TP = 1 reference run (same seeded logical weights)
+    cfg = E.Config("tiny", kvcache_block_size=16, num_kvcache_blocks=64)
+    sched, runner = E.Scheduler(cfg), E.ModelRunner(cfg)
+    runner.init_weights(1234, 0.05)
+    for p in prompts:
+        sched.add_sequence(p, E.SamplingParams(temperature=0.0, max_tokens=max_tokens, ignore_eos=True))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 2000
+    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, "tiny", prompts, max_tokens, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=60)
+    for rank, status, _ in res:
+        assert status == "ok", f"rank {rank}: {status}"
+    traces = [r[2] for r in res]
+    step, mismatched = 0, 0
+    while not sched.is_finished():
+        b = sched.schedule()
+        toks1, logits1 = runner.execute_model(b, return_logits=True)
+        tp_toks = traces[0][step][0]
+        for r in range(1, world):
+            assert np.array_equal(traces[r][step][0], tp_toks), "ranks disagree on the sampled tokens"
+        tp_logits = np.concatenate([traces[r][step][1] for r in range(world)], axis=1)
+        sigma = logits1.std()
+        # the all-reduce sums bf16-rounded per-rank partials: a few bf16 ulps per layer vs TP=1
+        assert np.abs(tp_logits - logits1).max() <= 0.1 * sigma, (step, np.abs(tp_logits - logits1).max() / sigma)
+        mismatched += int((tp_toks != toks1).sum())
+        sched.postprocess(tp_toks)   # teacher-force with the TP tokens so the two runs see the same inputs
+        step += 1
+    assert step == len(traces[0])
+    assert mismatched <= 0.1 * step * len(prompts)
