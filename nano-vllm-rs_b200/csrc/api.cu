@@ -1,5 +1,6 @@
 // api.cu — version / error plumbing of the C ABI (include/nvllm.h).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -24,6 +25,15 @@ int sm_count() {
     return 148;
   cached = n;
   return n;
+}
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("NVLLM_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
 }
 
 }  // namespace nvllm

@@ -44,6 +44,7 @@ inline int cuda_status(cudaError_t e, const char* what) {
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 int sm_count();  // api.cu (cached)
+bool pdl_enabled();  // api.cu: NVLLM_PDL=0 disables programmatic dependent launch (A/B measurements)
 
 }  // namespace nvllm
 
@@ -53,6 +54,30 @@ int sm_count();  // api.cu (cached)
 #ifdef __CUDACC__
 
 namespace nvllm {
+
+// ---- Programmatic dependent launch (PDL) -----------------------------------------------------------
+// Every kernel of the step is launched with cudaLaunchAttributeProgrammaticStreamSerialization: it may start while
+// its predecessor is still running.  Contract inside each kernel: pdl_launch_dependents() first (lets the successor
+// be scheduled), then only predecessor-independent work (barrier init, TMEM alloc, descriptor / weight prefetch),
+// then pdl_wait() before the first access to anything a previous kernel wrote or still reads.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 typedef __nv_bfloat16 bf16;
 typedef __nv_bfloat162 bf162;

@@ -21,6 +21,8 @@ template <bool HAS_RES>
 __global__ void __launch_bounds__(1024)
 add_rmsnorm_kernel(bf16* __restrict__ out, const bf16* __restrict__ x, bf16* __restrict__ residual,
                    const bf16* __restrict__ weight, int hidden, float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int row = blockIdx.x;
   const int nvec = hidden >> 3;
   const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<int64_t>(row) * hidden);
@@ -98,6 +100,8 @@ qknorm_rope_store_kernel(bf16* __restrict__ qkv, const int64_t* __restrict__ pos
                          int max_position, bf16* __restrict__ k_cache, bf16* __restrict__ v_cache,
                          const int32_t* __restrict__ slot_mapping, int block_size,
                          int64_t blk_stride, int64_t tok_stride, int64_t head_stride) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int EPL = D / 64;
   constexpr int HALF = D / 2;
   const int heads = H + 2 * Hkv;
@@ -206,6 +210,8 @@ namespace nvllm {
 // K8: out[t, j] = bf16( bf16(silu(g)) * u ) — two roundings, as the reference's two tensor ops.
 __global__ void __launch_bounds__(256)
 silu_mul_kernel(uint4* __restrict__ out, const uint4* __restrict__ x, int64_t total_vec, int inter_vec) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total_vec;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int64_t t = i / inter_vec;
@@ -240,6 +246,8 @@ __device__ __forceinline__ void gather_rows(uint4* __restrict__ out, const uint4
 __global__ void __launch_bounds__(256)
 embedding_gather_kernel(uint4* out, const uint4* table, const int64_t* __restrict__ ids, int rows,
                         int row_vec, int vocab) {
+  pdl_launch_dependents();
+  pdl_wait();
   gather_rows(out, table, rows, row_vec, [&](int i) {
     int64_t id = ids[i];
     return id < 0 ? 0 : (id >= vocab ? static_cast<int64_t>(vocab - 1) : id);
@@ -247,6 +255,8 @@ embedding_gather_kernel(uint4* out, const uint4* table, const int64_t* __restric
 }
 __global__ void __launch_bounds__(256)
 gather_last_kernel(uint4* out, const uint4* x, const int32_t* __restrict__ cu, int rows, int row_vec) {
+  pdl_launch_dependents();
+  pdl_wait();
   gather_rows(out, x, rows, row_vec, [&](int i) { return static_cast<int64_t>(cu[i + 1] - 1); });
 }
 
@@ -260,10 +270,35 @@ template <typename T>
 __global__ void __launch_bounds__(1024)
 argmax_kernel(int64_t* __restrict__ out_ids, float* __restrict__ out_max, const T* __restrict__ logits,
               int vocab, int64_t ld, int64_t vocab_offset) {
+  pdl_launch_dependents();
+  pdl_wait();
   const T* row = logits + blockIdx.x * ld;
   float best = -INFINITY;
   int bidx = 0x7fffffff;
-  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+  constexpr int VEC = 16 / sizeof(T);  // elements per 16-byte load
+  int head = 0;                        // scalar prologue up to the first 16-byte aligned element
+  {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(row) & 15u;
+    if (a) head = min(vocab, static_cast<int>((16 - a) / sizeof(T)));
+  }
+  for (int i = threadIdx.x; i < head; i += blockDim.x) {
+    const float v = to_f32<T>(row[i]);
+    if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
+  }
+  const int nvec = (vocab - head) / VEC;
+  const uint4* rv = reinterpret_cast<const uint4*>(row + head);
+  for (int j = threadIdx.x; j < nvec; j += blockDim.x) {
+    const uint4 q = ld_nc_16(rv + j);
+    T e[VEC];
+    *reinterpret_cast<uint4*>(e) = q;
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {  // ascending index inside the vector keeps the first-max rule
+      const float v = to_f32<T>(e[k]);
+      const int i = head + j * VEC + k;
+      if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
+    }
+  }
+  for (int i = head + nvec * VEC + threadIdx.x; i < vocab; i += blockDim.x) {
     const float v = to_f32<T>(row[i]);
     if (v > best || (v == best && i < bidx)) { best = v; bidx = i; }
   }
@@ -297,6 +332,8 @@ argmax_kernel(int64_t* __restrict__ out_ids, float* __restrict__ out_max, const 
 
 __global__ void argmax_combine_kernel(int64_t* __restrict__ out_ids, const float* __restrict__ all_max,
                                       const int64_t* __restrict__ all_ids, int tp, int batch) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
   float best = all_max[b];
@@ -355,13 +392,13 @@ extern "C" int nvllm_add_rmsnorm(void* out, const void* x, void* residual, const
   if (threads > 1024) threads = 1024;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (residual)
-    add_rmsnorm_kernel<true><<<num_tokens, threads, 0, st>>>(
-        static_cast<bf16*>(out), static_cast<const bf16*>(x), static_cast<bf16*>(residual),
-        static_cast<const bf16*>(weight), hidden, eps);
+    NVLLM_CUDA(launch_pdl(add_rmsnorm_kernel<true>, dim3(num_tokens), dim3(threads), 0, st, static_cast<bf16*>(out),
+                          static_cast<const bf16*>(x), static_cast<bf16*>(residual), static_cast<const bf16*>(weight),
+                          hidden, eps));
   else
-    add_rmsnorm_kernel<false><<<num_tokens, threads, 0, st>>>(
-        static_cast<bf16*>(out), static_cast<const bf16*>(x), nullptr,
-        static_cast<const bf16*>(weight), hidden, eps);
+    NVLLM_CUDA(launch_pdl(add_rmsnorm_kernel<false>, dim3(num_tokens), dim3(threads), 0, st, static_cast<bf16*>(out),
+                          static_cast<const bf16*>(x), static_cast<bf16*>(nullptr), static_cast<const bf16*>(weight),
+                          hidden, eps));
   NVLLM_LAUNCH_CHECK("add_rmsnorm_kernel");
   return 0;
 }
@@ -393,11 +430,11 @@ extern "C" int nvllm_qknorm_rope_store(void* qkv, const int64_t* positions, cons
   const unsigned blocks = static_cast<unsigned>((warps + 7) / 8);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define NVLLM_ROPE_LAUNCH(DD)                                                                         \
-  qknorm_rope_store_kernel<DD><<<blocks, 256, 0, st>>>(                                               \
+  NVLLM_CUDA(launch_pdl(qknorm_rope_store_kernel<DD>, dim3(blocks), dim3(256), 0, st,                 \
       static_cast<bf16*>(qkv), positions, cos_sin, static_cast<const bf16*>(q_norm_w),                \
       static_cast<const bf16*>(k_norm_w), eps, num_tokens, num_heads, num_kv_heads, max_position,     \
       static_cast<bf16*>(k_cache), static_cast<bf16*>(v_cache), slot_mapping, static_cast<int>(bs),   \
-      s_blk, s_tok, s_head)
+      s_blk, s_tok, s_head))
   if (head_dim == 128) NVLLM_ROPE_LAUNCH(128); else NVLLM_ROPE_LAUNCH(64);
 #undef NVLLM_ROPE_LAUNCH
   NVLLM_LAUNCH_CHECK("qknorm_rope_store_kernel");
@@ -423,8 +460,8 @@ extern "C" int nvllm_silu_mul(void* out, const void* x, int32_t num_tokens, int3
   if (num_tokens == 0) return 0;
   NVLLM_CHECK_ARG(out && x && aligned16(out) && aligned16(x), NVLLM_ERR_ALIGN, "silu_mul: pointers");
   const int64_t total = static_cast<int64_t>(num_tokens) * (inter / 8);
-  silu_mul_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<uint4*>(out), static_cast<const uint4*>(x), total, inter / 8);
+  NVLLM_CUDA(launch_pdl(silu_mul_kernel, dim3(grid_for(total, 256, 8)), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                        static_cast<uint4*>(out), static_cast<const uint4*>(x), total, inter / 8));
   NVLLM_LAUNCH_CHECK("silu_mul_kernel");
   return 0;
 }
@@ -438,8 +475,8 @@ extern "C" int nvllm_embedding_gather(void* out, const void* table, const int64_
   if (num_tokens == 0) return 0;
   NVLLM_CHECK_ARG(out && table && ids && aligned16(out) && aligned16(table), NVLLM_ERR_ALIGN,
                   "embedding_gather: pointers");
-  embedding_gather_kernel<<<(num_tokens + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<uint4*>(out), static_cast<const uint4*>(table), ids, num_tokens, hidden / 8, vocab);
+  NVLLM_CUDA(launch_pdl(embedding_gather_kernel, dim3((num_tokens + 7) / 8), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                        static_cast<uint4*>(out), static_cast<const uint4*>(table), ids, num_tokens, hidden / 8, vocab));
   NVLLM_LAUNCH_CHECK("embedding_gather_kernel");
   return 0;
 }
@@ -451,8 +488,8 @@ extern "C" int nvllm_gather_last_tokens(void* out, const void* x, const int32_t*
   if (batch == 0) return 0;
   NVLLM_CHECK_ARG(out && x && cu_seqlens_q && aligned16(out) && aligned16(x), NVLLM_ERR_ALIGN,
                   "gather_last_tokens: pointers");
-  gather_last_kernel<<<(batch + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<uint4*>(out), static_cast<const uint4*>(x), cu_seqlens_q, batch, hidden / 8);
+  NVLLM_CUDA(launch_pdl(gather_last_kernel, dim3((batch + 7) / 8), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                        static_cast<uint4*>(out), static_cast<const uint4*>(x), cu_seqlens_q, batch, hidden / 8));
   NVLLM_LAUNCH_CHECK("gather_last_kernel");
   return 0;
 }
@@ -465,9 +502,9 @@ extern "C" int nvllm_argmax(int64_t* out_ids, float* out_max, const void* logits
   NVLLM_CHECK_ARG(out_ids && logits, NVLLM_ERR_ARG, "argmax: NULL pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (logits_dtype == NVLLM_F32)
-    argmax_kernel<float><<<batch, 1024, 0, st>>>(out_ids, out_max, static_cast<const float*>(logits), vocab, ld, vocab_offset);
+    NVLLM_CUDA(launch_pdl(argmax_kernel<float>, dim3(batch), dim3(1024), 0, st, out_ids, out_max, static_cast<const float*>(logits), vocab, ld, vocab_offset));
   else if (logits_dtype == NVLLM_BF16)
-    argmax_kernel<bf16><<<batch, 1024, 0, st>>>(out_ids, out_max, static_cast<const bf16*>(logits), vocab, ld, vocab_offset);
+    NVLLM_CUDA(launch_pdl(argmax_kernel<bf16>, dim3(batch), dim3(1024), 0, st, out_ids, out_max, static_cast<const bf16*>(logits), vocab, ld, vocab_offset));
   else
     NVLLM_CHECK_ARG(false, NVLLM_ERR_DTYPE, "argmax: dtype %d", logits_dtype);
   NVLLM_LAUNCH_CHECK("argmax_kernel");
@@ -479,8 +516,8 @@ extern "C" int nvllm_argmax_combine(int64_t* out_ids, const float* all_max, cons
   NVLLM_CHECK_ARG(tp > 0 && batch >= 0, NVLLM_ERR_ARG, "argmax_combine: sizes");
   if (batch == 0) return 0;
   NVLLM_CHECK_ARG(out_ids && all_max && all_ids, NVLLM_ERR_ARG, "argmax_combine: NULL pointer");
-  argmax_combine_kernel<<<(batch + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      out_ids, all_max, all_ids, tp, batch);
+  NVLLM_CUDA(launch_pdl(argmax_combine_kernel, dim3((batch + 127) / 128), dim3(128), 0, static_cast<cudaStream_t>(stream),
+                        out_ids, all_max, all_ids, tp, batch));
   NVLLM_LAUNCH_CHECK("argmax_combine_kernel");
   return 0;
 }

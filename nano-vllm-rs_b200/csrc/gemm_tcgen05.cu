@@ -80,6 +80,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = K / C::BK;
+  pdl_launch_dependents();  // everything up to pdl_wait() below is independent of the previous kernel
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_x);
@@ -104,17 +105,34 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 
   if (warp == 0 && lane == 0) {
     // ===== TMA producer =====
+    // The weights do not depend on the previous kernel: the first ring of w tiles is requested BEFORE the
+    // programmatic-dependency wait, so their HBM latency hides behind the predecessor's tail; x follows after it.
+    const int pre = num_kb < STAGES ? num_kb : STAGES;
+    {
+      const int n_tile0 = blockIdx.x / num_m_tiles;
+      for (int kb = 0; kb < pre; ++kb) {
+        mbar_expect_tx(full_bar(kb), C::kStageBytes);
+        tma_load_2d(sB + kb * C::kBBytes, &tmap_w, full_bar(kb), kb * C::BK, n_tile0 * BN);
+      }
+    }
+    pdl_wait();
     int stage = 0;
     uint32_t phase = 0;
+    bool first = true;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
       for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(empty_bar(stage), phase ^ 1);
-        mbar_expect_tx(full_bar(stage), C::kStageBytes);
-        tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
-        tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
+        if (first && kb < pre) {  // w tile already in flight, barrier already armed
+          tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
+        } else {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), C::kStageBytes);
+          tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
+          tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
+        }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      first = false;
     }
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer (single thread) =====
@@ -143,6 +161,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     }
   } else if (warp >= 4) {
     // ===== epilogue: TMEM -> registers -> global =====
+    pdl_wait();              // y may still be read by an earlier kernel until the predecessor has completed
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -188,8 +207,8 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
   const int num_n_tiles = (N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * num_n_tiles;
   const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
-  kern<<<grid, 256, C::kSmemBytes, st>>>(tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles);
-  NVLLM_LAUNCH_CHECK("gemm_tcgen05_kernel");
+  NVLLM_CUDA(launch_pdl(kern, dim3(grid), dim3(256), C::kSmemBytes, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
+                        num_m_tiles, num_tiles));
   return 0;
 }
 
@@ -202,12 +221,15 @@ static int pick_bn(int M, int N) {
   if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
   const int sms = sm_count();
   const long mt = (M + 127) / 128;
-  const int cands[4] = {256, 128, 64, 32};
+  const int cands[4] = {32, 64, 128, 256};
+  // Small problems (decode): the narrowest tile that still fits in ONE wave — maximum number of CTAs streaming the
+  // weights concurrently, no second (serialised, latency-bound) pass over the persistent loop.
   for (int i = 0; i < 4; ++i) {
     const long tiles = mt * ((N + cands[i] - 1) / cands[i]);
-    if (tiles >= sms) return cands[i];
+    if (tiles <= sms) return cands[i];
   }
-  return 32;
+  // Large problems (prefill, LM head): widest tile = highest MMA efficiency and operand reuse.
+  return 256;
 }
 
 }  // namespace nvllm

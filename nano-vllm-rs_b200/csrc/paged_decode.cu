@@ -67,12 +67,14 @@ paged_decode_kernel(const DecodeParams p) {
   constexpr int KS = D / 16;  // k-steps of QK^T == m-tiles of PV
   extern __shared__ __align__(128) uint8_t smem[];
 
+  pdl_launch_dependents();
   const int split = blockIdx.x;
   const int kvh = blockIdx.y / p.ngrp;
   const int grp = blockIdx.y - kvh * p.ngrp;
   const int b = blockIdx.z;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_wait();  // q and the newest KV row were written by the previous kernel
   const int ctx = __ldg(p.ctx + b);
   const int gvalid = min(8, p.g - grp * 8);   // q heads handled by this CTA
   const int qh0 = kvh * p.g + grp * 8;         // first q head
@@ -277,6 +279,8 @@ paged_decode_kernel(const DecodeParams p) {
 // Combines the split-K partials: grid (H, B), D threads.
 template <int D>
 __global__ void __launch_bounds__(D) paged_decode_reduce_kernel(const DecodeParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int qh = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
   const int64_t base = (static_cast<int64_t>(b) * p.H + qh) * p.num_splits;
   float M = -INFINITY;
@@ -311,12 +315,9 @@ static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
     attr_set = true;
   }
   dim3 grid(p.num_splits, p.Hkv * p.ngrp, p.batch);
-  kern<<<grid, NWARPS * 32, C::kSmemBytes, stream>>>(p);
-  NVLLM_LAUNCH_CHECK("paged_decode_kernel");
-  if (p.num_splits > 1) {
-    paged_decode_reduce_kernel<D><<<dim3(p.H, p.batch), D, 0, stream>>>(p);
-    NVLLM_LAUNCH_CHECK("paged_decode_reduce_kernel");
-  }
+  NVLLM_CUDA(launch_pdl(kern, grid, dim3(NWARPS * 32), C::kSmemBytes, stream, p));
+  if (p.num_splits > 1)
+    NVLLM_CUDA(launch_pdl(paged_decode_reduce_kernel<D>, dim3(p.H, p.batch), dim3(D), 0, stream, p));
   return 0;
 }
 

@@ -61,6 +61,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   auto o_full = [&](int g) { return bars + (1 + 2 * STAGES + 2 + g) * 8; };
   const uint32_t tmem_slot = bars + kNumBars * 8;
 
+  pdl_launch_dependents();
+  pdl_wait();  // q / k / v (and the cache) come from the previous kernel
   const int seq = blockIdx.z, head = blockIdx.y, qblk = blockIdx.x;
   const int kvh = head / (p.H / p.Hkv);
   const int q0 = __ldg(p.cu_q + seq), Lq = __ldg(p.cu_q + seq + 1) - q0;
@@ -336,7 +338,7 @@ extern "C" int nvllm_varlen_prefill_attention(void* out, const void* q, const vo
   }
   (void)max_seqlen_k;
   dim3 grid((max_seqlen_q + 2 * pf::BM - 1) / (2 * pf::BM), num_heads, batch);
-  prefill_attn_kernel<<<grid, pf::kThreads, pf::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tq, tk, tv, p);
-  NVLLM_LAUNCH_CHECK("prefill_attn_kernel");
+  NVLLM_CUDA(launch_pdl(prefill_attn_kernel, grid, dim3(pf::kThreads), pf::kSmemBytes, static_cast<cudaStream_t>(stream),
+                        tq, tk, tv, p));
   return 0;
 }

@@ -16,6 +16,8 @@ store_kvcache_kernel(const uint4* __restrict__ k, const uint4* __restrict__ v,
                      int64_t kv_token_stride_v,  // in 16-byte vectors
                      int block_size, int hkv, int vec_per_head, int64_t block_stride_v,
                      int64_t token_stride_v, int64_t head_stride_v) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int vec_per_token = hkv * vec_per_head;
   const int64_t total = static_cast<int64_t>(num_tokens) * vec_per_token;
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
@@ -74,11 +76,11 @@ extern "C" int nvllm_store_kvcache(const void* k, const void* v, void* k_cache, 
   int64_t blocks = (total + threads - 1) / threads;
   const int64_t cap = static_cast<int64_t>(sm_count()) * 8;  // 8 resident CTAs of 256 threads / SM
   if (blocks > cap) blocks = cap;
-  store_kvcache_kernel<<<static_cast<unsigned>(blocks), threads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const uint4*>(k), static_cast<const uint4*>(v), static_cast<uint4*>(k_cache),
-      static_cast<uint4*>(v_cache), slot_mapping, num_tokens, kv_token_stride / 8,
-      layout->block_size, layout->num_kv_heads, vec_per_head, layout->block_stride / 8,
-      layout->token_stride / 8, layout->head_stride / 8);
+  NVLLM_CUDA(launch_pdl(store_kvcache_kernel, dim3(static_cast<unsigned>(blocks)), dim3(threads), 0,
+                        static_cast<cudaStream_t>(stream), static_cast<const uint4*>(k), static_cast<const uint4*>(v),
+                        static_cast<uint4*>(k_cache), static_cast<uint4*>(v_cache), slot_mapping, num_tokens,
+                        kv_token_stride / 8, layout->block_size, layout->num_kv_heads, vec_per_head,
+                        layout->block_stride / 8, layout->token_stride / 8, layout->head_stride / 8));
   NVLLM_LAUNCH_CHECK("store_kvcache_kernel");
   return 0;
 }
