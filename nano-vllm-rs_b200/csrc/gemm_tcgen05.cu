@@ -232,6 +232,18 @@ static int pick_bn(int M, int N) {
   return 256;
 }
 
+int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw,
+                       int64_t ldy, int out_dtype, cudaStream_t st);  // gemm_tcgen05_2cta.cu
+
+static bool use_2cta() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("NVLLM_GEMM_2CTA");  // A/B knob: 0 keeps every shape on the single-CTA kernel
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 }  // namespace nvllm
 
 extern "C" size_t nvllm_gemm_workspace_bytes(int32_t, int32_t, int32_t) { return 0; }
@@ -248,6 +260,8 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   NVLLM_CHECK_ARG(out_dtype == NVLLM_BF16 || out_dtype == NVLLM_F32, NVLLM_ERR_DTYPE, "gemm: out_dtype %d", out_dtype);
   if (m == 0) return 0;
   NVLLM_CHECK_ARG(y && x && w && aligned16(y) && aligned16(x) && aligned16(w), NVLLM_ERR_ALIGN, "gemm: pointers");
+  if (m > 128 && use_2cta())  // two or more 128-row tiles: CTA pairs share the w tile (gemm_tcgen05_2cta.cu)
+    return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, static_cast<cudaStream_t>(stream));
   const int bn = pick_bn(m, n);
   CUtensorMap tx, tw;
   if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;

@@ -12,8 +12,11 @@
 //   RG thread 0         MMA issuer:  S[128x64]  = Q[128x128] . K^T   (8 x tcgen05.mma M128 N64 K16, both K-major)
 //                                    Oj[128x128] = P[128x64] . V      (4 x tcgen05.mma M128 N128 K16, V MN-major)
 //   RG threads          S: tcgen05.ld -> online softmax in registers (row-local: no shuffles) -> P as bf16 into
-//                       shared memory in the SWIZZLE_128B K-major layout;  Oj: tcgen05.ld -> acc = acc*corr + Oj
-// TMEM: 512 columns = 2 RG x (S 64 + Oj 128, padded to 256).  Causal mask is bottom-right aligned
+//                       shared memory (double-buffered, SWIZZLE_128B K-major).  O accumulates IN TMEM across tiles
+//                       (the MMA adds into it); the running maximum is only refreshed when it grows by more than 2^8
+//                       (lazy rescale: then, and only then, O is read, scaled and written back with tcgen05.ld/st),
+//                       so the steady-state tile costs one S read and no O traffic at all.
+// TMEM: 512 columns = 2 RG x (S 64 + O 128, padded to 256).  Causal mask is bottom-right aligned
 // (row r of Lq sees keys <= Lk - Lq + r) so the same kernel serves Lq == Lk and suffix-over-prefix.
 #include "tc.cuh"
 
@@ -22,7 +25,7 @@ namespace nvllm {
 int check_layout(const nvllm_kv_layout* L);  // store_kvcache.cu
 
 namespace pf {
-constexpr int D = 128, BM = 128, BN = 64, STAGES = 3;
+constexpr int D = 128, BM = 128, BN = 64, STAGES = 2;
 constexpr int kQBytes = BM * D * 2;          // one RG's Q tile: 2 halves of [128 x 64]
 constexpr int kKVBytes = BN * D * 2;         // one K (or V) tile: 2 halves of [64 x 64]
 constexpr int kPBytes = BM * BN * 2;         // one RG's P tile [128 x 64]
@@ -30,7 +33,7 @@ constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kQBytes;
 constexpr int kSmemV = kSmemK + STAGES * kKVBytes;
 constexpr int kSmemP = kSmemV + STAGES * kKVBytes;
-constexpr int kSmemBar = kSmemP + 2 * kPBytes;
+constexpr int kSmemBar = kSmemP + 4 * kPBytes;  // 2 row groups x 2 P buffers
 constexpr int kNumBars = 1 + 2 * STAGES + 4;
 constexpr int kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;
 constexpr int kThreads = 288;
@@ -141,10 +144,9 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     const uint32_t tO = tS + 128;
     const uint32_t tS_mma = tmem_base + g * 256, tO_mma = tS_mma + 128;
     const uint32_t sQ = smem_base + kSmemQ + g * kQBytes;
-    const uint32_t sP = smem_base + kSmemP + g * kPBytes;
-    uint8_t* sP_gen = smem_gen + kSmemP + g * kPBytes;
     constexpr uint32_t idesc_s = umma_idesc_bf16(BM, BN, 0, 0);   // Q K-major, K K-major
     constexpr uint32_t idesc_o = umma_idesc_bf16(BM, D, 0, 1);    // P K-major, V MN-major
+    constexpr float kRescaleThreshold = 8.0f;                     // log2 units: P stays <= 2^8 between refreshes
 
     auto issue_s = [&](int j) {  // S = Q . K_j^T
       const int st = j % STAGES;
@@ -160,17 +162,15 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       umma_commit(s_full(g));
     };
 
-    float m_run = -INFINITY, l_run = 0.f;
-    float acc[D];
-#pragma unroll
-    for (int d = 0; d < D; ++d) acc[d] = 0.f;
-
+    float m_ref = -INFINITY, l_run = 0.f;  // m_ref: the (stale-by-design) maximum the exponentials are taken against
     if (issuer && n_my > 0) {
       mbar_wait(q_full, 0);
       issue_s(0);
     }
     for (int j = 0; j < n_my; ++j) {
       const int st = j % STAGES;
+      const uint32_t sP = smem_base + kSmemP + (g * 2 + (j & 1)) * kPBytes;
+      uint8_t* sP_gen = smem_gen + kSmemP + (g * 2 + (j & 1)) * kPBytes;
       // ---- softmax on S_j ---------------------------------------------------------------------
       mbar_wait(s_full(g), j & 1);
       tc_fence_after();
@@ -180,17 +180,37 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       tmem_ld_wait();
       const int kbase = j * BN;
       const bool need_mask = (kbase + BN - 1 > limit) || (kbase + BN > Lk);
-      float mx = m_run;
+      float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < 64; ++c) {
-        float s = __uint_as_float(sr[c >> 5][c & 31]);
-        if (need_mask && (kbase + c > limit || kbase + c >= Lk)) s = -INFINITY;
-        sr[c >> 5][c & 31] = __float_as_uint(s);
-        mx = fmaxf(mx, s);
+        float sv = __uint_as_float(sr[c >> 5][c & 31]);
+        if (need_mask && (kbase + c > limit || kbase + c >= Lk)) sv = -INFINITY;
+        sr[c >> 5][c & 31] = __float_as_uint(sv);
+        mx = fmaxf(mx, sv);
       }
-      const float m_safe = (mx == -INFINITY) ? 0.f : mx;
-      const float corr = fast_exp2((m_run - m_safe) * p.scale_log2);
-      const float moff = m_safe * p.scale_log2;
+      // lazy rescale: refresh the reference maximum only when this tile exceeds it by more than the threshold
+      const bool refresh = (mx - m_ref) * p.scale_log2 > kRescaleThreshold;  // also true for the first finite tile
+      float corr = 1.f;
+      if (refresh) {
+        corr = (m_ref == -INFINITY) ? 0.f : fast_exp2((m_ref - mx) * p.scale_log2);
+        m_ref = mx;
+        l_run *= corr;
+      }
+      if (j > 0 && __any_sync(0xffffffffu, refresh)) {  // tcgen05.ld/st are warp-collective: the whole warp takes part
+        mbar_wait(o_full(g), (j - 1) & 1);              // PV_{j-1} has finished accumulating into O
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) {
+          uint32_t orr[32];
+          tmem_ld_32x32b_x32(tO + c * 32, orr);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) orr[e] = __float_as_uint(__uint_as_float(orr[e]) * corr);
+          tmem_st_32x32b_x32(tO + c * 32, orr);
+        }
+        tmem_st_wait();
+      }
+      const float moff = (m_ref == -INFINITY) ? 0.f : m_ref * p.scale_log2;
       float lsum = 0.f;
 #pragma unroll
       for (int c8 = 0; c8 < 8; ++c8) {  // 8 chunks of 8 keys = 16 bytes of bf16 P each
@@ -206,12 +226,11 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         // SWIZZLE_128B K-major: row t at t*128 bytes, 16-byte chunk index XOR (row & 7)
         *reinterpret_cast<uint4*>(sP_gen + t * 128 + ((c8 ^ (t & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_run = l_run * corr + lsum;
-      m_run = mx;
+      l_run += lsum;
       tc_fence_before();
       fence_proxy_async();  // generic-proxy writes of P -> visible to the tensor core (async proxy)
       asm volatile("bar.sync %0, 128;\n" ::"r"(1 + g) : "memory");
-      // ---- O_j = P . V_j, then S_{j+1} ----------------------------------------------------------
+      // ---- O += P_j . V_j, then S_{j+1} -------------------------------------------------------------
       if (issuer) {
         tc_fence_after();
         const uint32_t sV = smem_base + kSmemV + st * kKVBytes;
@@ -220,14 +239,22 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const uint64_t ad = umma_desc_sw128(sP + ks * 32, 16, 1024);
           // V tile: rows = keys (k), 64 contiguous d per row; 2 MN groups (d halves) 8 KiB apart, 8 keys per 1 KiB
           const uint64_t bd = umma_desc_sw128(sV + ks * 2048, BN * 128, 1024);
-          umma_bf16_ss(tO_mma, ad, bd, idesc_o, ks != 0);
+          umma_bf16_ss(tO_mma, ad, bd, idesc_o, (j | ks) != 0);
         }
         umma_commit(o_full(g));
         umma_commit(kv_empty(st));
         if (j + 1 < n_my) issue_s(j + 1);
       }
-      // ---- acc = acc * corr + O_j ------------------------------------------------------------------
-      mbar_wait(o_full(g), j & 1);
+      // P buffer (j & 1) is rewritten at tile j + 2: PV_j must have retired by then
+      if (j + 2 < n_my && !(j + 1 > 0 && false)) { /* ordering handled below */ }
+      if (j >= 1) {
+        // cheap in steady state: PV_{j-1} was issued a whole tile ago
+        mbar_wait(o_full(g), (j - 1) & 1);
+      }
+    }
+    float acc[D];
+    if (n_my > 0) {
+      mbar_wait(o_full(g), (n_my - 1) & 1);
       tc_fence_after();
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
@@ -235,7 +262,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         tmem_ld_32x32b_x32(tO + c * 32, orr);
         tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 32; ++e) acc[c * 32 + e] = fmaf(acc[c * 32 + e], corr, __uint_as_float(orr[e]));
+        for (int e = 0; e < 32; ++e) acc[c * 32 + e] = __uint_as_float(orr[e]);
       }
       tc_fence_before();
     }
