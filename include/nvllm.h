@@ -198,6 +198,16 @@ int nvllm_comm_destroy(nvllm_comm* comm);
 int nvllm_allreduce(nvllm_comm* comm, void* buf, size_t count, int32_t dtype, void* stream);
 int nvllm_allgather(nvllm_comm* comm, const void* send, void* recv, size_t bytes_per_rank,
                     void* stream);
+/* Symmetric (peer-mapped) memory: a collective call — every rank allocates `bytes`, the CUDA IPC handles are exchanged
+ * through the communicator and each peer's region is mapped over NVLink.  *local_base = this rank's region. */
+int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base);
+/* C1 fused with what always follows it (RowParallelLinear all-reduce TODO linear.rs:236 + the residual add and RMSNorm
+ * of Qwen3Layer::forward, qwen3.rs:382-385,389): one two-shot kernel over NVLink peer memory —
+ *   residual <- bf16(residual + bf16(sum over ranks of x));  out <- rmsnorm(residual) * weight     on EVERY rank.
+ * out, x, residual: [num_tokens, hidden] bf16 buffers at identical offsets inside every rank's symmetric region.
+ * Bit-identical results on all ranks (each row is reduced once, by its owner, in fixed rank order). */
+int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
+                                int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream);
 
 /* Deterministic seeded weight init shared bit-for-bit with the CPU oracle (oracle/weights.py):
  * element i of tensor `tensor_id` = bf16( (sum of the four 16-bit fields of

@@ -260,7 +260,10 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   NVLLM_CHECK_ARG(out_dtype == NVLLM_BF16 || out_dtype == NVLLM_F32, NVLLM_ERR_DTYPE, "gemm: out_dtype %d", out_dtype);
   if (m == 0) return 0;
   NVLLM_CHECK_ARG(y && x && w && aligned16(y) && aligned16(x) && aligned16(w), NVLLM_ERR_ALIGN, "gemm: pointers");
-  if (m > 128 && use_2cta())  // two or more 128-row tiles: CTA pairs share the w tile (gemm_tcgen05_2cta.cu)
+  // two or more 128-row tiles: CTA pairs share the w tile (gemm_tcgen05_2cta.cu).  Exception (measured): skinny
+  // problems with a very long K (8B down_proj at decode, M = 512, K = 12288 > 2N) stream x from L2 once per n-tile and
+  // do better with more, narrower single-CTA tiles until a split-K variant exists.
+  if (m > 128 && use_2cta() && !(m <= 512 && k > 2 * n))
     return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, static_cast<cudaStream_t>(stream));
   const int bn = pick_bn(m, n);
   CUtensorMap tx, tw;

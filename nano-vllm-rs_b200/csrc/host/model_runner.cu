@@ -106,6 +106,7 @@ struct nvllm_runner {
   int last_decode_b = 0, last_decode_splits = 1;
   std::vector<int32_t> last_ctx;
   bool weights_ready = false;
+  bool fused_tp = false;  // h / normed / proj live in NVLink-mapped symmetric memory; all-reduce fused with add + RMSNorm
 
   ~nvllm_runner() {
     for (auto& g : graphs)
@@ -202,7 +203,20 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   }
   // activations
   const size_t T = max_tokens;
-  RUN(dalloc(&h, T * hidden)); RUN(dalloc(&normed, T * hidden)); RUN(dalloc(&proj, T * hidden));
+  if (tp > 1) {
+    const char* e = getenv("NVLLM_FUSED_TP");  // A/B knob: 0 = ncclAllReduce + separate add_rmsnorm
+    if (!(e && e[0] == '0')) {
+      const size_t one = (T * hidden * 2 + 255) & ~static_cast<size_t>(255);
+      void* base = nullptr;
+      if (nvllm_comm_symm_alloc(comm, 3 * one, &base) == 0) {
+        h = static_cast<bf16*>(base);
+        normed = reinterpret_cast<bf16*>(static_cast<uint8_t*>(base) + one);
+        proj = reinterpret_cast<bf16*>(static_cast<uint8_t*>(base) + 2 * one);
+        fused_tp = true;
+      }
+    }
+  }
+  if (!fused_tp) { RUN(dalloc(&h, T * hidden)); RUN(dalloc(&normed, T * hidden)); RUN(dalloc(&proj, T * hidden)); }
   RUN(dalloc(&qkv, T * qkv_dim)); RUN(dalloc(&attn, T * H * D));
   RUN(dalloc(&gate_up, T * 2 * inter)); RUN(dalloc(&act, T * inter));
   RUN(dalloc(&last_hidden, static_cast<size_t>(max_seqs) * hidden));
@@ -396,13 +410,26 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
     ++launches;
     return nvllm_gemm_bf16(y, x, w, N, n, k, k, k, ldy, out_dt, nullptr, 0, st);
   };
+  // h += all-reduce(proj); normed = rmsnorm(h) * w — the reference's RowParallelLinear all-reduce TODO (linear.rs:236)
+  // followed by the residual add + norm: one fused kernel over NVLink peer memory, or NCCL + add_rmsnorm.
+  auto add_norm = [&](const bf16* w) -> int {
+    if (tp > 1 && fused_tp) {
+      ++launches;
+      return nvllm_allreduce_add_rmsnorm(comm, normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+    }
+    if (tp > 1) { RUN(nvllm_allreduce(comm, proj, static_cast<size_t>(N) * hidden, NVLLM_BF16, st)); ++launches; }
+    ++launches;
+    return nvllm_add_rmsnorm(normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+  };
   RUN(nvllm_embedding_gather(h, embed, d_ids, N, hidden, vocab, NVLLM_BF16, st)); ++launches;
   const int splits = is_prefill ? 1 : nvllm_paged_decode_choose_splits(N, H, Hkv, table_cap * layout.block_size);
   if (!is_prefill) last_decode_splits = splits;
   for (int l = 0; l < layers; ++l) {
     const LayerWeights& w = lw[l];
     // input_layernorm; for l > 0 fused with the residual add of the previous MLP output (qwen3.rs:389 -> :378)
-    RUN(nvllm_add_rmsnorm(normed, l == 0 ? h : proj, l == 0 ? nullptr : h, w.input_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches;
+    // (and, under TP, with the all-reduce of that output: see add_norm below)
+    if (l == 0) { RUN(nvllm_add_rmsnorm(normed, h, nullptr, w.input_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches; }
+    else RUN(add_norm(w.input_ln));
     RUN(gemm(qkv, normed, w.qkv, qkv_dim, hidden, qkv_dim, NVLLM_BF16));
     // q/k norm + RoPE in place, K/V of this step into the cache (store before attention: note N2)
     RUN(nvllm_qknorm_rope_store(qkv, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr, cfg.qk_norm ? w.k_norm : nullptr, eps,
@@ -418,14 +445,12 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
                                          &layout, scale, NVLLM_BF16, st)); ++launches;
     }
     RUN(gemm(proj, attn, w.o, hidden, HD, hidden, NVLLM_BF16));
-    if (tp > 1) { RUN(nvllm_allreduce(comm, proj, static_cast<size_t>(N) * hidden, NVLLM_BF16, st)); ++launches; }  // linear.rs:236
-    RUN(nvllm_add_rmsnorm(normed, proj, h, w.post_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches;                  // qwen3.rs:382-385
+    RUN(add_norm(w.post_ln));                                                                                          // qwen3.rs:382-385
     RUN(gemm(gate_up, normed, w.gate_up, 2 * inter, hidden, 2 * inter, NVLLM_BF16));
     RUN(nvllm_silu_mul(act, gate_up, N, inter, NVLLM_BF16, st)); ++launches;
     RUN(gemm(proj, act, w.down, hidden, inter, hidden, NVLLM_BF16));
-    if (tp > 1) { RUN(nvllm_allreduce(comm, proj, static_cast<size_t>(N) * hidden, NVLLM_BF16, st)); ++launches; }
   }
-  RUN(nvllm_add_rmsnorm(normed, proj, h, final_norm, N, hidden, eps, NVLLM_BF16, st)); ++launches;                   // qwen3.rs:389,501
+  RUN(add_norm(final_norm));                                                                                           // qwen3.rs:389,501
   const bf16* head_in = normed;
   int rows = N;
   if (is_prefill) {  // only the last token of each sequence feeds the head (embed_head.rs:250-289)

@@ -12,7 +12,7 @@
 //   RG thread 0         MMA issuer:  S[128x64]  = Q[128x128] . K^T   (8 x tcgen05.mma M128 N64 K16, both K-major)
 //                                    Oj[128x128] = P[128x64] . V      (4 x tcgen05.mma M128 N128 K16, V MN-major)
 //   RG threads          S: tcgen05.ld -> online softmax in registers (row-local: no shuffles) -> P as bf16 into
-//                       shared memory (double-buffered, SWIZZLE_128B K-major).  O accumulates IN TMEM across tiles
+//                       shared memory (SWIZZLE_128B K-major).  O accumulates IN TMEM across tiles
 //                       (the MMA adds into it); the running maximum is only refreshed when it grows by more than 2^8
 //                       (lazy rescale: then, and only then, O is read, scaled and written back with tcgen05.ld/st),
 //                       so the steady-state tile costs one S read and no O traffic at all.
@@ -25,7 +25,7 @@ namespace nvllm {
 int check_layout(const nvllm_kv_layout* L);  // store_kvcache.cu
 
 namespace pf {
-constexpr int D = 128, BM = 128, BN = 64, STAGES = 2;
+constexpr int D = 128, BM = 128, BN = 64, STAGES = 3;
 constexpr int kQBytes = BM * D * 2;          // one RG's Q tile: 2 halves of [128 x 64]
 constexpr int kKVBytes = BN * D * 2;         // one K (or V) tile: 2 halves of [64 x 64]
 constexpr int kPBytes = BM * BN * 2;         // one RG's P tile [128 x 64]
@@ -33,7 +33,7 @@ constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kQBytes;
 constexpr int kSmemV = kSmemK + STAGES * kKVBytes;
 constexpr int kSmemP = kSmemV + STAGES * kKVBytes;
-constexpr int kSmemBar = kSmemP + 4 * kPBytes;  // 2 row groups x 2 P buffers
+constexpr int kSmemBar = kSmemP + 2 * kPBytes;
 constexpr int kNumBars = 1 + 2 * STAGES + 4;
 constexpr int kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;
 constexpr int kThreads = 288;
@@ -169,10 +169,14 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     }
     for (int j = 0; j < n_my; ++j) {
       const int st = j % STAGES;
-      const uint32_t sP = smem_base + kSmemP + (g * 2 + (j & 1)) * kPBytes;
-      uint8_t* sP_gen = smem_gen + kSmemP + (g * 2 + (j & 1)) * kPBytes;
+      const uint32_t sP = smem_base + kSmemP + g * kPBytes;
+      uint8_t* sP_gen = smem_gen + kSmemP + g * kPBytes;
       // ---- softmax on S_j ---------------------------------------------------------------------
       mbar_wait(s_full(g), j & 1);
+      // tcgen05.mma of one thread retire in issue order and S_j was issued after PV_{j-1}: this wait is free, it only
+      // consumes the phase (every o_full phase is waited exactly once, in order).  After it, O is quiescent and the
+      // P buffer may be rewritten.
+      if (j > 0) mbar_wait(o_full(g), (j - 1) & 1);
       tc_fence_after();
       uint32_t sr[2][32];
       tmem_ld_32x32b_x32(tS, sr[0]);
@@ -197,8 +201,6 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         l_run *= corr;
       }
       if (j > 0 && __any_sync(0xffffffffu, refresh)) {  // tcgen05.ld/st are warp-collective: the whole warp takes part
-        mbar_wait(o_full(g), (j - 1) & 1);              // PV_{j-1} has finished accumulating into O
-        tc_fence_after();
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
           uint32_t orr[32];
@@ -244,12 +246,6 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         umma_commit(o_full(g));
         umma_commit(kv_empty(st));
         if (j + 1 < n_my) issue_s(j + 1);
-      }
-      // P buffer (j & 1) is rewritten at tile j + 2: PV_j must have retired by then
-      if (j + 2 < n_my && !(j + 1 > 0 && false)) { /* ordering handled below */ }
-      if (j >= 1) {
-        // cheap in steady state: PV_{j-1} was issued a whole tile ago
-        mbar_wait(o_full(g), (j - 1) & 1);
       }
     }
     float acc[D];
