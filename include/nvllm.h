@@ -127,6 +127,14 @@ size_t nvllm_gemm_workspace_bytes(int32_t m, int32_t n, int32_t k);
 int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
                     int64_t ldx, int64_t ldw, int64_t ldy, int32_t out_dtype, void* workspace,
                     size_t workspace_bytes, void* stream);
+/* MergedColumnParallelLinear::forward followed by SiluAndMul::forward (linear.rs:437-439, activation.rs:46-63) in one
+ * call: out[M, inter] = silu(x . Wgate^T) * (x . Wup^T), w_gate_up = [Wgate | Wup] packed row-wise ([2*inter, K]).
+ * For M > 128 the activation runs in the GEMM epilogue (CTA pairs: one CTA stages the gate rows, its peer the up rows)
+ * and the [M, 2*inter] intermediate never reaches HBM; smaller M uses `workspace` (>= M*2*inter*2 bytes) for it.
+ * Same rounding points as nvllm_gemm_bf16 + nvllm_silu_mul (bit-identical results). */
+int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_gate_up, int32_t m, int32_t inter, int32_t k,
+                             int64_t ldx, int64_t ldw, int64_t ldout, void* workspace, size_t workspace_bytes,
+                             void* stream);
 /* Plain CUDA-core version of the same contract; test infrastructure for the kernel above (used to
  * check large shapes on the device where the CPU oracle is too slow).  Never on the product path. */
 int nvllm_gemm_bf16_simt(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,

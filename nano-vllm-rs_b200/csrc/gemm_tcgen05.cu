@@ -235,6 +235,9 @@ static int pick_bn(int M, int N) {
 int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw,
                        int64_t ldy, int out_dtype, cudaStream_t st);  // gemm_tcgen05_2cta.cu
 
+int gemm_silu_2cta_dispatch(void* y, const void* x, const void* w, int m, int inter, int k, int64_t ldx, int64_t ldw,
+                            int64_t ldy, cudaStream_t st);  // gemm_tcgen05_2cta.cu
+
 static bool use_2cta() {
   static int v = -1;
   if (v < 0) {
@@ -282,4 +285,27 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
       NVLLM_GEMM_CASE(32);
   }
 #undef NVLLM_GEMM_CASE
+}
+
+// MergedColumnParallelLinear::forward + SiluAndMul::forward in one call (linear.rs:437-439 + activation.rs:46-63).
+extern "C" int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_gate_up, int32_t m, int32_t inter,
+                                        int32_t k, int64_t ldx, int64_t ldw, int64_t ldout, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  using namespace nvllm;
+  NVLLM_CHECK_ARG(m >= 0 && inter > 0 && k > 0 && k % 64 == 0 && inter % 8 == 0, NVLLM_ERR_ARG,
+                  "gemm_silu_mul: m=%d inter=%d k=%d (k %% 64, inter %% 8)", m, inter, k);
+  NVLLM_CHECK_ARG(ldx >= k && ldw >= k && ldout >= inter && ldx % 8 == 0 && ldw % 8 == 0 && ldout % 8 == 0,
+                  NVLLM_ERR_ALIGN, "gemm_silu_mul: leading dimensions");
+  if (m == 0) return 0;
+  NVLLM_CHECK_ARG(out && x && w_gate_up && aligned16(out) && aligned16(x) && aligned16(w_gate_up), NVLLM_ERR_ALIGN,
+                  "gemm_silu_mul: pointers");
+  if (m > 128 && use_2cta() && inter % 128 == 0)  // fused epilogue on CTA pairs: the [m, 2*inter] tensor never exists
+    return gemm_silu_2cta_dispatch(out, x, w_gate_up, m, inter, k, ldx, ldw, ldout, static_cast<cudaStream_t>(stream));
+  // small batches: plain GEMM into the workspace, then the SiLU*mul kernel
+  const size_t need = static_cast<size_t>(m) * 2 * inter * 2;
+  NVLLM_CHECK_ARG(workspace && workspace_bytes >= need && aligned16(workspace), NVLLM_ERR_WORKSPACE,
+                  "gemm_silu_mul: workspace %zu < %zu bytes", workspace_bytes, need);
+  NVLLM_CHECK_ARG(ldout == inter, NVLLM_ERR_ARG, "gemm_silu_mul: unfused path needs a contiguous output");
+  if (int rc = nvllm_gemm_bf16(workspace, x, w_gate_up, m, 2 * inter, k, ldx, ldw, 2 * inter, NVLLM_BF16, nullptr, 0, stream)) return rc;
+  return nvllm_silu_mul(out, workspace, m, inter, NVLLM_BF16, stream);
 }

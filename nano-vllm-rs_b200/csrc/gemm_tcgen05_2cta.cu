@@ -46,7 +46,11 @@ __device__ __forceinline__ void store_row32_2(OutT* dst, const uint32_t (&r)[32]
   }
 }
 
-template <int BN, typename OutT>
+// SILU == true: w is the packed [gate (N rows) | up (N rows)] matrix of MergedColumnParallelLinear (linear.rs:421-433);
+// the leader CTA stages BN/2 gate rows, its peer the matching BN/2 up rows, so accumulator columns [0, BN/2) are gate and
+// [BN/2, BN) are up for the same BN/2 output features, and the epilogue writes y[:, n_tile*BN/2 + c] = silu(gate)*up
+// (SiluAndMul::forward, activation.rs:46-63) without the [M, 2N] intermediate ever reaching HBM.  N = output features.
+template <int BN, typename OutT, bool SILU>
 __global__ void __launch_bounds__(256, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                          OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles) {
@@ -103,7 +107,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
         mbar_wait(empty_bar(stage), phase ^ 1);
         if (leader) mbar_expect_tx(full_bar(stage), 2 * C::kStageBytes);
         tma_load_2d_cg2(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM + rank * C::BM_CTA);
-        tma_load_2d_cg2(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN + rank * (BN / 2));
+        tma_load_2d_cg2(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK,
+                        SILU ? static_cast<int>(rank) * N + n_tile * (BN / 2) : n_tile * BN + static_cast<int>(rank) * (BN / 2));
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -144,13 +149,35 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
       tc_fence_after();
       const int row = m_tile * C::BM + rank * C::BM_CTA + q * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      if constexpr (SILU) {
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        const int col0 = n_tile * BN + c * 32;
-        if (row < M && col0 < N) store_row32_2<OutT>(y + row * ldy + col0, r, col0, N);
+        for (int c = 0; c < BN / 64; ++c) {
+          uint32_t g[32], u[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, g);
+          tmem_ld_32x32b_x32(taddr + BN / 2 + c * 32, u);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            // same rounding points as the unfused path: gate_up is a bf16 tensor, silu(gate) is a bf16 tensor
+            const uint32_t gb = pack_bf16x2(__uint_as_float(g[e]), __uint_as_float(g[e + 1]));
+            const uint32_t ub = pack_bf16x2(__uint_as_float(u[e]), __uint_as_float(u[e + 1]));
+            const float g0 = bf16_lo(gb), g1 = bf16_hi(gb);
+            const uint32_t sb = pack_bf16x2(g0 / (1.0f + expf(-g0)), g1 / (1.0f + expf(-g1)));
+            g[e] = __float_as_uint(bf16_lo(sb) * bf16_lo(ub));
+            g[e + 1] = __float_as_uint(bf16_hi(sb) * bf16_hi(ub));
+          }
+          const int col0 = n_tile * (BN / 2) + c * 32;
+          if (row < M && col0 < N) store_row32_2<OutT>(y + row * ldy + col0, g, col0, N);
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, r);
+          tmem_ld_wait();
+          const int col0 = n_tile * BN + c * 32;
+          if (row < M && col0 < N) store_row32_2<OutT>(y + row * ldy + col0, r, col0, N);
+        }
       }
       tc_fence_before();
       mbar_arrive_cluster(tempty_bar(acc), 0);  // tell the leader this CTA's half of the accumulator is drained
@@ -166,18 +193,18 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
   }
 }
 
-template <int BN, typename OutT>
+template <int BN, typename OutT, bool SILU = false>
 static int launch_gemm2(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy,
                         cudaStream_t st) {
   using C = Gemm2Cfg<BN>;
-  auto kern = gemm_tcgen05_2cta_kernel<BN, OutT>;
+  auto kern = gemm_tcgen05_2cta_kernel<BN, OutT, SILU>;
   static bool attr_set = false;
   if (!attr_set) {
     NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
   const int num_m_tiles = (M + C::BM - 1) / C::BM;
-  const int num_n_tiles = (N + BN - 1) / BN;
+  const int num_n_tiles = SILU ? (N + BN / 2 - 1) / (BN / 2) : (N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * num_n_tiles;
   const int max_clusters = sm_count() / 2;
   const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
@@ -240,6 +267,22 @@ int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int 
       NVLLM_G2(64);
   }
 #undef NVLLM_G2
+}
+
+// y[M, inter] = silu(x . Wgate^T) * (x . Wup^T) with w = [Wgate | Wup] packed row-wise ([2*inter, K]).
+int gemm_silu_2cta_dispatch(void* y, const void* x, const void* w, int m, int inter, int k, int64_t ldx, int64_t ldw,
+                            int64_t ldy, cudaStream_t st) {
+  // accumulator tile BN covers BN/2 output features; reuse the tile heuristic on the 2*inter accumulator columns
+  const int bn = pick_bn_2cta(m, 2 * inter);
+  NVLLM_CHECK_ARG(inter % (bn / 2) == 0 || true, NVLLM_ERR_ARG, "gemm_silu: inter");
+  CUtensorMap tx, tw;
+  if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
+  if (int rc = make_tmap_bf16_2d(&tw, w, 2 * static_cast<int64_t>(inter), k, ldw, bn / 2)) return rc;
+  switch (bn) {
+    case 256: return launch_gemm2<256, bf16, true>(tx, tw, y, m, inter, k, ldy, st);
+    case 128: return launch_gemm2<128, bf16, true>(tx, tw, y, m, inter, k, ldy, st);
+    default: return launch_gemm2<64, bf16, true>(tx, tw, y, m, inter, k, ldy, st);
+  }
 }
 
 }  // namespace nvllm

@@ -61,7 +61,7 @@ struct DecodeCfg {
 };
 
 template <int D, int STAGES, int NWARPS>
-__global__ void __launch_bounds__(NWARPS * 32, (DecodeCfg<D, STAGES, NWARPS>::kSmemBytes <= 110 * 1024) ? 2 : 1)
+__global__ void __launch_bounds__(NWARPS * 32, (DecodeCfg<D, STAGES, NWARPS>::kSmemBytes <= 72 * 1024) ? 3 : (DecodeCfg<D, STAGES, NWARPS>::kSmemBytes <= 110 * 1024) ? 2 : 1)
 paged_decode_kernel(const DecodeParams p) {
   using C = DecodeCfg<D, STAGES, NWARPS>;
   constexpr int KS = D / 16;  // k-steps of QK^T == m-tiles of PV
@@ -429,7 +429,8 @@ extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void
     switch (decode_cfg_id()) {
       case 1: return launch_decode<128, 4, 4>(p, st);
       case 2: return launch_decode<128, 3, 8>(p, st);
-      case 3: return launch_decode<128, 2, 4>(p, st);
+      case 3: return launch_decode<128, 2, 4>(p, st);   // 64 KiB smem: 3 CTAs / SM
+      case 4: return launch_decode<128, 4, 2>(p, st);   // 2 warps x 4 stages, 64 KiB: 3 CTAs / SM
       default: return launch_decode<128, 3, 4>(p, st);
     }
   }

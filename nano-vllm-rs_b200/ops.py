@@ -102,6 +102,19 @@ def gemm_bf16(x, w, out=None, out_dtype=torch.bfloat16, simt=False):
     return out
 
 
+def gemm_silu_mul(x, w_gate_up, out=None):
+    """MergedColumnParallelLinear::forward + SiluAndMul::forward fused (linear.rs:437-439, activation.rs:46-63)."""
+    _need(x, torch.bfloat16, "x"); _need(w_gate_up, torch.bfloat16, "w_gate_up")
+    M, K = x.shape
+    inter = w_gate_up.shape[0] // 2
+    if out is None:
+        out = torch.empty((M, inter), dtype=torch.bfloat16, device=x.device)
+    ws = torch.empty((M, 2 * inter), dtype=torch.bfloat16, device=x.device)
+    check(_ffi.lib().nvllm_gemm_silu_mul_bf16(_p(out), _p(x), _p(w_gate_up), M, inter, K, x.stride(0), w_gate_up.stride(0),
+                                              out.stride(0), _p(ws), ws.numel() * 2, _stream()))
+    return out
+
+
 def add_rmsnorm(x, weight, eps, residual=None, out=None):
     """RMSNorm::forward (layernorm.rs:50-97). With `residual`, it is updated in place to bf16(residual + x)."""
     _need(x, torch.bfloat16, "x")

@@ -81,3 +81,19 @@ def test_gemm_strided_views(cuda):
     ref = O.linear(xb[:, 128:384], wb[:, 256:512])
     assert_close(to_np_f32(out[:, 200:400]), ref, ATOL, RTOL, "strided gemm")
     assert float(out[:, :200].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("m,inter,k", [(256, 3072, 1024), (300, 1536, 512), (512, 12288, 4096), (64, 3072, 1024), (129, 256, 128)])
+def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k):
+    """gate_up GEMM with the SiLU*mul epilogue (M > 128: CTA-pair kernel) is bit-identical to GEMM + silu_mul."""
+    from nano_vllm_rs_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(m + inter + k)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn((2 * inter, k), generator=g, device=cuda) * 0.05).to(torch.bfloat16)
+    fused = ops.gemm_silu_mul(x, w)
+    ref = ops.silu_mul(ops.gemm_bf16(x, w))
+    torch.cuda.synchronize()
+    assert torch.equal(fused, ref)
+    if m * inter * k < 2 ** 28:   # and against the CPU oracle where it is cheap
+        want = O.silu_and_mul(O.linear(to_np_f32(x), to_np_f32(w)))
+        assert_close(to_np_f32(fused), want, ATOL, 2 ** -6, "gemm_silu_mul vs oracle")
