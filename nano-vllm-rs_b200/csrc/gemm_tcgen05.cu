@@ -59,7 +59,9 @@ __device__ __forceinline__ void store_row32<float>(float* dst, const uint32_t (&
   }
 }
 
-template <int BN, typename OutT>
+// SILU == true: w = [gate (N rows) | up (N rows)]; the B tile is staged as BN/2 gate rows + the matching BN/2 up rows and
+// the epilogue writes y[:, n_tile*BN/2 + c] = silu(gate) * up (see gemm_tcgen05_2cta.cu for the CTA-pair variant).
+template <int BN, typename OutT, bool SILU>
 __global__ void __launch_bounds__(256, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles) {
@@ -107,12 +109,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     // ===== TMA producer =====
     // The weights do not depend on the previous kernel: the first ring of w tiles is requested BEFORE the
     // programmatic-dependency wait, so their HBM latency hides behind the predecessor's tail; x follows after it.
+    auto load_w = [&](int stage, int kb, int n_tile) {
+      if constexpr (SILU) {
+        tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * (BN / 2));
+        tma_load_2d(sB + stage * C::kBBytes + (BN / 2) * 128, &tmap_w, full_bar(stage), kb * C::BK, N + n_tile * (BN / 2));
+      } else {
+        tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
+      }
+    };
     const int pre = num_kb < STAGES ? num_kb : STAGES;
     {
       const int n_tile0 = blockIdx.x / num_m_tiles;
       for (int kb = 0; kb < pre; ++kb) {
         mbar_expect_tx(full_bar(kb), C::kStageBytes);
-        tma_load_2d(sB + kb * C::kBBytes, &tmap_w, full_bar(kb), kb * C::BK, n_tile0 * BN);
+        load_w(kb, kb, n_tile0);
       }
     }
     pdl_wait();
@@ -128,7 +138,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           mbar_wait(empty_bar(stage), phase ^ 1);
           mbar_expect_tx(full_bar(stage), C::kStageBytes);
           tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
-          tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
+          load_w(stage, kb, n_tile);
         }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -171,13 +181,34 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       tc_fence_after();
       const int row = m_tile * C::BM + q * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+      if constexpr (SILU) {
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        const int col0 = n_tile * BN + c * 32;
-        if (row < M && col0 < N) store_row32<OutT>(y + row * ldy + col0, r, col0, N);
+        for (int c = 0; c < BN / 64; ++c) {
+          uint32_t g[32], u[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, g);
+          tmem_ld_32x32b_x32(taddr + BN / 2 + c * 32, u);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {  // rounding points of the unfused path: bf16 gate_up, bf16 silu(gate)
+            const uint32_t gb = pack_bf16x2(__uint_as_float(g[e]), __uint_as_float(g[e + 1]));
+            const uint32_t ub = pack_bf16x2(__uint_as_float(u[e]), __uint_as_float(u[e + 1]));
+            const float g0 = bf16_lo(gb), g1 = bf16_hi(gb);
+            const uint32_t sb = pack_bf16x2(g0 / (1.0f + expf(-g0)), g1 / (1.0f + expf(-g1)));
+            g[e] = __float_as_uint(bf16_lo(sb) * bf16_lo(ub));
+            g[e + 1] = __float_as_uint(bf16_hi(sb) * bf16_hi(ub));
+          }
+          const int col0 = n_tile * (BN / 2) + c * 32;
+          if (row < M && col0 < N) store_row32<OutT>(y + row * ldy + col0, g, col0, N);
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, r);
+          tmem_ld_wait();
+          const int col0 = n_tile * BN + c * 32;
+          if (row < M && col0 < N) store_row32<OutT>(y + row * ldy + col0, r, col0, N);
+        }
       }
       tc_fence_before();
       mbar_arrive(tempty_bar(acc));
@@ -193,18 +224,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   }
 }
 
-template <int BN, typename OutT>
+template <int BN, typename OutT, bool SILU = false>
 static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy,
                        cudaStream_t st) {
   using C = GemmCfg<BN>;
-  auto kern = gemm_tcgen05_kernel<BN, OutT>;
+  auto kern = gemm_tcgen05_kernel<BN, OutT, SILU>;
   static bool attr_set = false;
   if (!attr_set) {
     NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
   const int num_m_tiles = (M + C::BM - 1) / C::BM;
-  const int num_n_tiles = (N + BN - 1) / BN;
+  const int num_n_tiles = SILU ? (N + BN / 2 - 1) / (BN / 2) : (N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * num_n_tiles;
   const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
   NVLLM_CUDA(launch_pdl(kern, dim3(grid), dim3(256), C::kSmemBytes, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
@@ -238,6 +269,19 @@ int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int 
 int gemm_silu_2cta_dispatch(void* y, const void* x, const void* w, int m, int inter, int k, int64_t ldx, int64_t ldw,
                             int64_t ldy, cudaStream_t st);  // gemm_tcgen05_2cta.cu
 
+static bool use_2cta();
+// CTA pairs pay off once there are at least two 256-row tiles or the problem is large enough to fill the machine with
+// 256 x 256 tiles; between 129 and 511 rows the single-CTA kernel (more, narrower, single-wave tiles) measured faster
+// inside the decode step.  Skinny problems with a very long K (8B down_proj at decode: M = 512, K = 12288 > 2N) stream x
+// from L2 once per n-tile and also do better on single-CTA tiles until a split-K variant exists.
+static bool want_2cta(int m, int n, int k) {
+  if (m <= 128 || !use_2cta()) return false;
+  const long big_tiles = static_cast<long>((m + 255) / 256) * ((n + 255) / 256);
+  if (m < 512 && big_tiles < sm_count() / 2) return false;
+  if (m <= 512 && k > 2 * n) return false;
+  return true;
+}
+
 static bool use_2cta() {
   static int v = -1;
   if (v < 0) {
@@ -263,10 +307,7 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   NVLLM_CHECK_ARG(out_dtype == NVLLM_BF16 || out_dtype == NVLLM_F32, NVLLM_ERR_DTYPE, "gemm: out_dtype %d", out_dtype);
   if (m == 0) return 0;
   NVLLM_CHECK_ARG(y && x && w && aligned16(y) && aligned16(x) && aligned16(w), NVLLM_ERR_ALIGN, "gemm: pointers");
-  // two or more 128-row tiles: CTA pairs share the w tile (gemm_tcgen05_2cta.cu).  Exception (measured): skinny
-  // problems with a very long K (8B down_proj at decode, M = 512, K = 12288 > 2N) stream x from L2 once per n-tile and
-  // do better with more, narrower single-CTA tiles until a split-K variant exists.
-  if (m > 128 && use_2cta() && !(m <= 512 && k > 2 * n))
+  if (want_2cta(m, n, k))
     return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, static_cast<cudaStream_t>(stream));
   const int bn = pick_bn(m, n);
   CUtensorMap tx, tw;
@@ -299,9 +340,21 @@ extern "C" int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_
   if (m == 0) return 0;
   NVLLM_CHECK_ARG(out && x && w_gate_up && aligned16(out) && aligned16(x) && aligned16(w_gate_up), NVLLM_ERR_ALIGN,
                   "gemm_silu_mul: pointers");
-  if (m > 128 && use_2cta() && inter % 128 == 0)  // fused epilogue on CTA pairs: the [m, 2*inter] tensor never exists
-    return gemm_silu_2cta_dispatch(out, x, w_gate_up, m, inter, k, ldx, ldw, ldout, static_cast<cudaStream_t>(stream));
-  // small batches: plain GEMM into the workspace, then the SiLU*mul kernel
+  (void)workspace; (void)workspace_bytes;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (inter % 128 == 0) {  // fused epilogue: the [m, 2*inter] tensor never exists
+    if (want_2cta(m, 2 * inter, k)) return gemm_silu_2cta_dispatch(out, x, w_gate_up, m, inter, k, ldx, ldw, ldout, st);
+    const int bn = pick_bn(m, 2 * inter) < 64 ? 64 : pick_bn(m, 2 * inter);
+    CUtensorMap tx, tw;
+    if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
+    if (int rc = make_tmap_bf16_2d(&tw, w_gate_up, 2 * static_cast<int64_t>(inter), k, ldw, bn / 2)) return rc;
+    switch (bn) {
+      case 256: return launch_gemm<256, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
+      case 128: return launch_gemm<128, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
+      default: return launch_gemm<64, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
+    }
+  }
+  // odd intermediate sizes: plain GEMM into the workspace, then the SiLU*mul kernel
   const size_t need = static_cast<size_t>(m) * 2 * inter * 2;
   NVLLM_CHECK_ARG(workspace && workspace_bytes >= need && aligned16(workspace), NVLLM_ERR_WORKSPACE,
                   "gemm_silu_mul: workspace %zu < %zu bytes", workspace_bytes, need);

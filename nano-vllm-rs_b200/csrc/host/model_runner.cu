@@ -446,10 +446,10 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
     }
     RUN(gemm(proj, attn, w.o, hidden, HD, hidden, NVLLM_BF16));
     RUN(add_norm(w.post_ln));                                                                                          // qwen3.rs:382-385
-    // gate_up GEMM with the SiLU*mul in its epilogue for N > 128 (otherwise GEMM + activation kernel)
+    // gate_up GEMM with the SiLU*mul in its epilogue (MergedColumnParallelLinear + SiluAndMul, qwen3.rs:307-310)
     RUN(nvllm_gemm_silu_mul_bf16(act, normed, w.gate_up, N, inter, hidden, hidden, hidden, inter, gate_up,
                                  static_cast<size_t>(max_tokens) * 2 * inter * 2, st));
-    launches += (N > 128 && inter % 128 == 0) ? 1 : 2;
+    launches += (inter % 128 == 0) ? 1 : 2;
     RUN(gemm(proj, act, w.down, hidden, inter, hidden, NVLLM_BF16));
   }
   RUN(add_norm(final_norm));                                                                                           // qwen3.rs:389,501

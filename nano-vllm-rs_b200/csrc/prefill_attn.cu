@@ -16,7 +16,11 @@
 //                       (the MMA adds into it); the running maximum is only refreshed when it grows by more than 2^8
 //                       (lazy rescale: then, and only then, O is read, scaled and written back with tcgen05.ld/st),
 //                       so the steady-state tile costs one S read and no O traffic at all.
-// TMEM: 512 columns = 2 RG x (S 64 + O 128, padded to 256).  Causal mask is bottom-right aligned
+//                       S (TMEM) and P (smem) are double-buffered per group: S_{j+1} = Q.K_{j+1}^T is issued BEFORE the
+//                       softmax of tile j and PV_j right after it, so a group's CUDA-core work never waits for its own MMAs.
+//                       exp2: half of the elements go through MUFU.EX2, half through a degree-3 polynomial on the FMA
+//                       pipe (MUFU, 16/clk/SM, would otherwise cap the kernel at the MMA rate).
+// TMEM: 512 columns = 2 RG x (S0 64 + S1 64 + O 128).  Causal mask is bottom-right aligned
 // (row r of Lq sees keys <= Lk - Lq + r) so the same kernel serves Lq == Lk and suffix-over-prefix.
 #include "tc.cuh"
 
@@ -33,8 +37,8 @@ constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kQBytes;
 constexpr int kSmemV = kSmemK + STAGES * kKVBytes;
 constexpr int kSmemP = kSmemV + STAGES * kKVBytes;
-constexpr int kSmemBar = kSmemP + 2 * kPBytes;
-constexpr int kNumBars = 1 + 2 * STAGES + 4;
+constexpr int kSmemBar = kSmemP + 4 * kPBytes;  // 2 row groups x 2 P buffers
+constexpr int kNumBars = 1 + 2 * STAGES + 8;
 constexpr int kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;
 constexpr int kThreads = 288;
 }  // namespace pf
@@ -60,8 +64,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   const uint32_t q_full = bars;
   auto kv_full = [&](int s) { return bars + (1 + s) * 8; };
   auto kv_empty = [&](int s) { return bars + (1 + STAGES + s) * 8; };
-  auto s_full = [&](int g) { return bars + (1 + 2 * STAGES + g) * 8; };
-  auto o_full = [&](int g) { return bars + (1 + 2 * STAGES + 2 + g) * 8; };
+  auto s_full = [&](int g, int b) { return bars + (1 + 2 * STAGES + g * 2 + b) * 8; };      // S buffer b of group g written
+  auto o_full = [&](int g, int b) { return bars + (1 + 2 * STAGES + 4 + g * 2 + b) * 8; };  // PV that read P buffer b retired
   const uint32_t tmem_slot = bars + kNumBars * 8;
 
   pdl_launch_dependents();
@@ -88,7 +92,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k); tma_prefetch_desc(&tmap_v);
     mbar_init(q_full, 1);
     for (int s = 0; s < STAGES; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 2); }
-    for (int g = 0; g < 2; ++g) { mbar_init(s_full(g), 1); mbar_init(o_full(g), 1); }
+    for (int g = 0; g < 2; ++g)
+      for (int b = 0; b < 2; ++b) { mbar_init(s_full(g, b), 1); mbar_init(o_full(g, b), 1); }
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc<512>(tmem_slot);
@@ -140,15 +145,15 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     const bool issuer = t == 0;
     const int row = qblk * 2 * BM + g * BM + t;  // row within the sequence's queries
     const int limit = shift + row;               // last visible key index
-    const uint32_t tS = tmem_base + g * 256 + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    const uint32_t tO = tS + 128;
-    const uint32_t tS_mma = tmem_base + g * 256, tO_mma = tS_mma + 128;
+    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t tS_mma = tmem_base + g * 256, tO_mma = tS_mma + 128;   // S buffers at +0 / +64, O at +128
+    const uint32_t tO = tO_mma + lane_off;
     const uint32_t sQ = smem_base + kSmemQ + g * kQBytes;
     constexpr uint32_t idesc_s = umma_idesc_bf16(BM, BN, 0, 0);   // Q K-major, K K-major
     constexpr uint32_t idesc_o = umma_idesc_bf16(BM, D, 0, 1);    // P K-major, V MN-major
     constexpr float kRescaleThreshold = 8.0f;                     // log2 units: P stays <= 2^8 between refreshes
 
-    auto issue_s = [&](int j) {  // S = Q . K_j^T
+    auto issue_s = [&](int j) {  // S_j = Q . K_j^T into S buffer j & 1
       const int st = j % STAGES;
       mbar_wait(kv_full(st), (j / STAGES) & 1);
       tc_fence_after();
@@ -157,9 +162,20 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       for (int ks = 0; ks < D / 16; ++ks) {
         const uint64_t ad = umma_desc_sw128(sQ + (ks >> 2) * (BM * 128) + (ks & 3) * 32, 16, 1024);
         const uint64_t bd = umma_desc_sw128(sK + (ks >> 2) * (BN * 128) + (ks & 3) * 32, 16, 1024);
-        umma_bf16_ss(tS_mma, ad, bd, idesc_s, ks != 0);
+        umma_bf16_ss(tS_mma + (j & 1) * BN, ad, bd, idesc_s, ks != 0);
       }
-      umma_commit(s_full(g));
+      umma_commit(s_full(g, j & 1));
+    };
+    // 2^x for x <= 0 on the FMA pipe: x = n + f, f in [0, 1); 2^f by a degree-3 minimax polynomial (rel. err 1e-4, far
+    // below bf16's 2^-9), 2^n by adding n to the exponent field.
+    auto exp2_poly = [](float x) {
+      x = fmaxf(x, -126.f);
+      const float n = floorf(x);
+      const float f = x - n;
+      float pfr = fmaf(f, 0.0790209f, 0.2241543f);
+      pfr = fmaf(pfr, f, 0.6965186f);
+      pfr = fmaf(pfr, f, 0.9998430f);
+      return __int_as_float(__float_as_int(pfr) + (static_cast<int>(n) << 23));
     };
 
     float m_ref = -INFINITY, l_run = 0.f;  // m_ref: the (stale-by-design) maximum the exponentials are taken against
@@ -168,30 +184,31 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       issue_s(0);
     }
     for (int j = 0; j < n_my; ++j) {
-      const int st = j % STAGES;
-      const uint32_t sP = smem_base + kSmemP + g * kPBytes;
-      uint8_t* sP_gen = smem_gen + kSmemP + g * kPBytes;
-      // ---- softmax on S_j ---------------------------------------------------------------------
-      mbar_wait(s_full(g), j & 1);
-      // tcgen05.mma of one thread retire in issue order and S_j was issued after PV_{j-1}: this wait is free, it only
-      // consumes the phase (every o_full phase is waited exactly once, in order).  After it, O is quiescent and the
-      // P buffer may be rewritten.
-      if (j > 0) mbar_wait(o_full(g), (j - 1) & 1);
+      const int st = j % STAGES, b = j & 1;
+      const uint32_t sP = smem_base + kSmemP + (g * 2 + b) * kPBytes;
+      uint8_t* sP_gen = smem_gen + kSmemP + (g * 2 + b) * kPBytes;
+      mbar_wait(s_full(g, b), (j >> 1) & 1);     // S_j is in TMEM
+      // S_{j+1} goes to the other S buffer (its previous content, S_{j-1}, was consumed before the last bar.sync):
+      // the tensor core computes it while this group works on tile j.
+      if (issuer && j + 1 < n_my) issue_s(j + 1);
       tc_fence_after();
+      // ---- softmax on S_j ---------------------------------------------------------------------
       uint32_t sr[2][32];
+      const uint32_t tS = tS_mma + b * BN + lane_off;
       tmem_ld_32x32b_x32(tS, sr[0]);
       tmem_ld_32x32b_x32(tS + 32, sr[1]);
       tmem_ld_wait();
       const int kbase = j * BN;
       const bool need_mask = (kbase + BN - 1 > limit) || (kbase + BN > Lk);
-      float mx = -INFINITY;
+      if (need_mask) {
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        float sv = __uint_as_float(sr[c >> 5][c & 31]);
-        if (need_mask && (kbase + c > limit || kbase + c >= Lk)) sv = -INFINITY;
-        sr[c >> 5][c & 31] = __float_as_uint(sv);
-        mx = fmaxf(mx, sv);
+        for (int c = 0; c < 64; ++c)
+          if (kbase + c > limit || kbase + c >= Lk) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
       }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // 4 independent chains
+#pragma unroll
+      for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       // lazy rescale: refresh the reference maximum only when this tile exceeds it by more than the threshold
       const bool refresh = (mx - m_ref) * p.scale_log2 > kRescaleThreshold;  // also true for the first finite tile
       float corr = 1.f;
@@ -201,6 +218,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         l_run *= corr;
       }
       if (j > 0 && __any_sync(0xffffffffu, refresh)) {  // tcgen05.ld/st are warp-collective: the whole warp takes part
+        mbar_wait(o_full(g, (j - 1) & 1), ((j - 1) >> 1) & 1);  // PV_{j-1} retired: O is quiescent
+        tc_fence_after();
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
           uint32_t orr[32];
@@ -212,27 +231,30 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         }
         tmem_st_wait();
       }
+      if (j >= 2) mbar_wait(o_full(g, b), ((j - 2) >> 1) & 1);  // PV_{j-2} retired: P buffer b may be rewritten
       const float moff = (m_ref == -INFINITY) ? 0.f : m_ref * p.scale_log2;
-      float lsum = 0.f;
+      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c8 = 0; c8 < 8; ++c8) {  // 8 chunks of 8 keys = 16 bytes of bf16 P each
         uint32_t pk[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int c = c8 * 8 + e * 2;
-          const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff));
-          lsum += p0 + p1;
+          const float a0 = fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff);
+          const float a1 = fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff);
+          const float p0 = fast_exp2(a0);   // MUFU
+          const float p1 = exp2_poly(a1);   // FMA pipe
+          ls4[e] += p0 + p1;
           pk[e] = pack_bf16x2(p0, p1);
         }
         // SWIZZLE_128B K-major: row t at t*128 bytes, 16-byte chunk index XOR (row & 7)
         *reinterpret_cast<uint4*>(sP_gen + t * 128 + ((c8 ^ (t & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      l_run += lsum;
+      l_run += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
       tc_fence_before();
       fence_proxy_async();  // generic-proxy writes of P -> visible to the tensor core (async proxy)
       asm volatile("bar.sync %0, 128;\n" ::"r"(1 + g) : "memory");
-      // ---- O += P_j . V_j, then S_{j+1} -------------------------------------------------------------
+      // ---- O += P_j . V_j ------------------------------------------------------------------------
       if (issuer) {
         tc_fence_after();
         const uint32_t sV = smem_base + kSmemV + st * kKVBytes;
@@ -243,14 +265,14 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const uint64_t bd = umma_desc_sw128(sV + ks * 2048, BN * 128, 1024);
           umma_bf16_ss(tO_mma, ad, bd, idesc_o, (j | ks) != 0);
         }
-        umma_commit(o_full(g));
+        umma_commit(o_full(g, b));
         umma_commit(kv_empty(st));
-        if (j + 1 < n_my) issue_s(j + 1);
       }
     }
     float acc[D];
     if (n_my > 0) {
-      mbar_wait(o_full(g), (n_my - 1) & 1);
+      if (n_my >= 2) mbar_wait(o_full(g, (n_my - 2) & 1), ((n_my - 2) >> 1) & 1);
+      mbar_wait(o_full(g, (n_my - 1) & 1), ((n_my - 1) >> 1) & 1);
       tc_fence_after();
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
