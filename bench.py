@@ -31,7 +31,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 MODELS = {"qwen3-0.6b": dict(seqs=256, prompt=512, decode=512, blocks_per_seq=4),
-          "qwen3-8b": dict(seqs=512, prompt=1024, decode=1024, blocks_per_seq=8)}
+          "qwen3-8b": dict(seqs=512, prompt=1024, decode=1024, blocks_per_seq=8),
+          # BASELINE.json configs[4]: Qwen3-32B TP=8, 64 seqs at 32K context (long-context split-K paged decode stress)
+          "qwen3-32b": dict(seqs=64, prompt=32256, decode=512, blocks_per_seq=129)}
 
 
 def parse():
@@ -40,7 +42,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=64)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--model", default=None, help="override the workload model (qwen3-0.6b | qwen3-8b)")
+    ap.add_argument("--model", default=None, help="override the workload model (qwen3-0.6b | qwen3-8b | qwen3-32b)")
     ap.add_argument("--seqs", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--eager", action="store_true", help="enforce_eager (no CUDA graphs)")
@@ -222,7 +224,8 @@ def main():
     max_len = prompt + W + K + 8
     nblk = B * ((max_len + 255) // 256) + 8
     cfg = E.Config(model, tensor_parallel_size=world, tp_rank=rank, max_num_seqs=max(B, 8), num_kvcache_blocks=nblk,
-                   max_model_len=max(4096, ((max_len + 255) // 256) * 256), enforce_eager=int(args.eager))
+                   max_model_len=max(4096, ((max_len + 255) // 256) * 256), enforce_eager=int(args.eager),
+                   max_position_embeddings=max(40960, ((max_len + 255) // 256) * 256))
     eng = E.LLMEngine(cfg, comm=comm, seed=1234, std=0.02)
     rng = np.random.default_rng(1234)                      # token stream seed 1234, ids mod vocab
     sp = E.SamplingParams(temperature=0.0, max_tokens=W + 2 * K + 64, ignore_eos=True)

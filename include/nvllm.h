@@ -129,8 +129,9 @@ int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n,
                     size_t workspace_bytes, void* stream);
 /* MergedColumnParallelLinear::forward followed by SiluAndMul::forward (linear.rs:437-439, activation.rs:46-63) in one
  * call: out[M, inter] = silu(x . Wgate^T) * (x . Wup^T), w_gate_up = [Wgate | Wup] packed row-wise ([2*inter, K]).
- * For M > 128 the activation runs in the GEMM epilogue (CTA pairs: one CTA stages the gate rows, its peer the up rows)
- * and the [M, 2*inter] intermediate never reaches HBM; smaller M uses `workspace` (>= M*2*inter*2 bytes) for it.
+ * When inter %% 128 == 0 the activation runs in the GEMM epilogue (the B tile holds BN/2 gate rows + the matching BN/2
+ * up rows; with CTA pairs one CTA stages the gate rows, its peer the up rows) and the [M, 2*inter] intermediate never
+ * reaches HBM; other sizes use `workspace` (>= M*2*inter*2 bytes) for it.
  * Same rounding points as nvllm_gemm_bf16 + nvllm_silu_mul (bit-identical results). */
 int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_gate_up, int32_t m, int32_t inter, int32_t k,
                              int64_t ldx, int64_t ldw, int64_t ldout, void* workspace, size_t workspace_bytes,
@@ -211,7 +212,10 @@ int nvllm_allgather(nvllm_comm* comm, const void* send, void* recv, size_t bytes
 int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base);
 /* C1 fused with what always follows it (RowParallelLinear all-reduce TODO linear.rs:236 + the residual add and RMSNorm
  * of Qwen3Layer::forward, qwen3.rs:382-385,389): one two-shot kernel over NVLink peer memory —
- *   residual <- bf16(residual + bf16(sum over ranks of x));  out <- rmsnorm(residual) * weight     on EVERY rank.
+ *   residual <- bf16(residual + bf16(sum over ranks of x));  out <- rmsnorm(residual) * weight.
+ * `out` is complete on EVERY rank afterwards; `residual` is updated only for the rows this rank owns
+ * (rows [rank*R, (rank+1)*R), R = ceil(num_tokens / world)) — it is a row-sharded stream whose only readers are
+ * subsequent calls of this function with the same num_tokens.
  * out, x, residual: [num_tokens, hidden] bf16 buffers at identical offsets inside every rank's symmetric region.
  * Bit-identical results on all ranks (each row is reduced once, by its owner, in fixed rank order). */
 int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,

@@ -44,7 +44,7 @@ typedef struct nvllm_config {
 
 /* Fills the reference defaults (config.rs:54-71) and a named Qwen3 architecture:
  * "qwen3-0.6b" | "qwen3-8b" | "qwen3-32b" | "reference-default" (qwen3.rs:70-89: hidden 4096, 32 layers, 32/32 heads,
- * theta 1e4, no qk-norm) | "tiny" (2-layer test model). */
+ * theta 1e4, no qk-norm) | "tiny" / "tiny-tp8" (2-layer test models). */
 int nvllm_config_init(nvllm_config* cfg, const char* arch);
 /* Config::validate (config.rs:83-119) + Qwen3Config::validate (qwen3.rs:106-123) on the fields above. */
 int nvllm_config_validate(const nvllm_config* cfg);

@@ -108,7 +108,8 @@ struct FusedArParams {
 //   shot 1  rank r owns rows [r*R, (r+1)*R): it reads those rows of every rank's partial sums over NVLink (16-byte
 //           peer loads, fixed rank order -> bit-identical on every rank), rounds the sum to bf16 (the all-reduced tensor),
 //           adds the residual (bf16 tensor add), normalises in f32;
-//   shot 2  it writes the new residual rows and the normed rows into EVERY rank's buffers (peer stores).
+//   shot 2  it writes the normed rows into EVERY rank's buffer (peer stores); the new residual rows stay on the owner
+//           (the residual stream is row-sharded across ranks between the fused kernels of one forward).
 // Flags in the control block: `ready` (my partial sums are complete / my buffers may be overwritten) before shot 1,
 // `done` (all my remote writes are visible) before the kernel may complete.  Epoch counters live in device memory and
 // advance inside the kernel, so a captured CUDA graph can replay it.
@@ -182,11 +183,11 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           ow[j] = pack_bf16x2(v[k][2 * j] * inv * bf16_lo(ww[j]), v[k][2 * j + 1] * inv * bf16_hi(ww[j]));
-        const uint4 sres = make_uint4(sw[k][0], sw[k][1], sw[k][2], sw[k][3]);
-        for (int q = 0; q < p.world; ++q) {  // shot 2: broadcast both rows to every rank
-          *reinterpret_cast<uint4*>(p.peer[q] + p.res_off + roff + i * 16) = sres;
+        // The residual stream stays ROW-SHARDED: its only readers are these fused kernels, and row `row` is always
+        // reduced by this rank, so the new residual is written locally only (halves the NVLink write traffic).
+        *reinterpret_cast<uint4*>(p.peer[p.rank] + p.res_off + roff + i * 16) = make_uint4(sw[k][0], sw[k][1], sw[k][2], sw[k][3]);
+        for (int q = 0; q < p.world; ++q)  // shot 2: broadcast the normed row to every rank
           *reinterpret_cast<uint4*>(p.peer[q] + p.out_off + roff + i * 16) = o;
-        }
       }
     }
     __syncthreads();  // red / s_inv reuse

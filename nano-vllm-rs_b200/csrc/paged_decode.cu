@@ -348,15 +348,25 @@ extern "C" int nvllm_paged_decode_choose_splits(int32_t batch, int32_t num_heads
   const int g = num_heads / num_kv_heads;
   const int ngrp = (g + 7) / 8;
   const long base = static_cast<long>(batch) * num_kv_heads * ngrp;
-  const int sms = nvllm::sm_count();
-  if (base >= 2L * sms) return 1;
-  long want = (3L * sms + base - 1) / base;        // ~3 CTAs per SM
-  long by_len = max_context_len / 256;             // keep >= 256 tokens per split
-  if (by_len < 1) by_len = 1;
-  if (want > by_len) want = by_len;
-  if (want > 64) want = 64;
-  if (want < 1) want = 1;
-  return static_cast<int>(want);
+  const long slots = 2L * nvllm::sm_count();  // 2 resident CTAs per SM
+  long max_s = max_context_len / 256;          // keep >= 256 tokens per split
+  if (max_s < 1) max_s = 1;
+  if (max_s > 64) max_s = 64;
+  if (base >= 8 * slots) return 1;             // many waves already: quantisation loss < 1/8 wave
+  // Wave-aware choice: the grid runs in waves of `slots` CTAs; pick the split count whose last wave is fullest (e.g.
+  // 512 CTAs on 296 slots = 1.73 waves -> 4 splits = 6.9 waves), discounted by the cost of the partials
+  // (each split adds one fp32 [H, D] partial per sequence + the reduce kernel).
+  int best = 1;
+  double best_score = -1.0;
+  for (long sp = 1; sp <= max_s; ++sp) {
+    const long ctas = base * sp;
+    const long waves = (ctas + slots - 1) / slots;
+    double eff = static_cast<double>(ctas) / static_cast<double>(waves * slots);
+    if (sp > 1) eff *= (1.0 - 0.02 - 0.004 * static_cast<double>(sp));
+    if (eff > best_score + 1e-9) { best_score = eff; best = static_cast<int>(sp); }
+    if (ctas >= 8 * slots) break;
+  }
+  return best;
 }
 
 extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache,

@@ -49,7 +49,7 @@ def _tp_worker(rank, world, port, arch, prompts, max_tokens, q):
         q.put((rank, "fail: " + traceback.format_exc(), None))
 
 
-@pytest.mark.parametrize("world", [2])
+@pytest.mark.parametrize("world", [2, 4, 8])
 def test_tp_engine_matches_single_gpu(cuda, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
@@ -58,8 +58,9 @@ def test_tp_engine_matches_single_gpu(cuda, world):
     rng = np.random.default_rng(5)
     prompts = [rng.integers(0, 1024, n).tolist() for n in (7, 40, 16, 33)]
     max_tokens = 12
+    arch = "tiny" if world == 2 else "tiny-tp8"
     # TP = 1 reference run (same seeded logical weights)
-    cfg = E.Config("tiny", kvcache_block_size=16, num_kvcache_blocks=64)
+    cfg = E.Config(arch, kvcache_block_size=16, num_kvcache_blocks=64)
     sched, runner = E.Scheduler(cfg), E.ModelRunner(cfg)
     runner.init_weights(1234, 0.05)
     for p in prompts:
@@ -67,7 +68,7 @@ def test_tp_engine_matches_single_gpu(cuda, world):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29600 + os.getpid() % 2000
-    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, "tiny", prompts, max_tokens, q)) for r in range(world)]
+    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, arch, prompts, max_tokens, q)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
