@@ -4,24 +4,20 @@
 // 321-339: per-sequence loop, O(L^2) host-built mask, dense matmul) and flash_attention_varlen_with_cache
 // (:211-222, prefill of the uncached suffix against the paged prefix).
 //
-// One CTA = 256 query rows of one (sequence, head): two "row groups" (RG) of 128 threads, one query row per
-// thread, sharing the K/V tiles of the KV head.  While one RG runs its softmax on CUDA cores the tensor core
-// executes the other RG's MMAs (ping-pong).
-//   warp 8 (one lane)   TMA producer: Q once (2 x 128 x 128), then K/V tiles of 64 keys through a STAGES ring;
-//                       dense K/V via a 2-D map, paged K/V via a 4-D map (d, token, head, block) + block_tables
-//   RG thread 0         MMA issuer:  S[128x64]  = Q[128x128] . K^T   (8 x tcgen05.mma M128 N64 K16, both K-major)
-//                                    Oj[128x128] = P[128x64] . V      (4 x tcgen05.mma M128 N128 K16, V MN-major)
-//   RG threads          S: tcgen05.ld -> online softmax in registers (row-local: no shuffles) -> P as bf16 into
-//                       shared memory (SWIZZLE_128B K-major).  O accumulates IN TMEM across tiles
-//                       (the MMA adds into it); the running maximum is only refreshed when it grows by more than 2^8
-//                       (lazy rescale: then, and only then, O is read, scaled and written back with tcgen05.ld/st),
-//                       so the steady-state tile costs one S read and no O traffic at all.
-//                       S (TMEM) and P (smem) are double-buffered per group: S_{j+1} = Q.K_{j+1}^T is issued BEFORE the
-//                       softmax of tile j and PV_j right after it, so a group's CUDA-core work never waits for its own MMAs.
-//                       exp2: half of the elements go through MUFU.EX2, half through a degree-3 polynomial on the FMA
-//                       pipe (MUFU, 16/clk/SM, would otherwise cap the kernel at the MMA rate).
-// TMEM: 512 columns = 2 RG x (S0 64 + S1 64 + O 128).  Causal mask is bottom-right aligned
-// (row r of Lq sees keys <= Lk - Lq + r) so the same kernel serves Lq == Lk and suffix-over-prefix.
+// One CTA = 256 query rows of one (sequence, head): two row groups (RG) of 128 threads, one query row per thread
+// (== one TMEM lane), sharing the K/V tiles of the KV head; KV tiles of 128 keys.
+//   warp 8 (one lane)   TMA producer: Q once (2 x 128 x 128), then K_0, V_0, K_1, V_1, ... through a ring of NSLOT
+//                       32 KiB slots; dense K/V via a 2-D map, paged K/V via a 4-D map (d, token, head, block) + block_tables
+//   warp 9 (one lane)   MMA issuer for both groups: S = Q . K^T (8 x tcgen05.mma M128 N128 K16, both operands K-major in
+//                       shared memory) and O += P . V (8 x tcgen05.mma with A = P read from TENSOR MEMORY, V MN-major)
+//   RG threads          tcgen05.ld S row -> row max -> exp2 (half on MUFU, half by a polynomial on the FMA pipe) ->
+//                       P as packed bf16 written BACK INTO TMEM over the S columns (tcgen05.st; each thread only touches its
+//                       own lane, so no cross-thread hazard) -> mbarrier arrive.  No shared-memory round trip for P.
+//                       O accumulates in TMEM across tiles; the reference maximum is refreshed lazily (only when a tile
+//                       exceeds it by 2^8), and only then is O read, scaled and written back.
+// While one group runs its softmax the tensor core executes the other group's MMAs.
+// TMEM: 512 columns = 2 RG x (S/P 128 + O 128).  Causal mask is bottom-right aligned (row r of Lq sees keys <= Lk - Lq + r)
+// so the same kernel serves Lq == Lk and suffix-over-prefix.  CTAs are ordered longest-first.
 #include "tc.cuh"
 
 namespace nvllm {
@@ -29,18 +25,15 @@ namespace nvllm {
 int check_layout(const nvllm_kv_layout* L);  // store_kvcache.cu
 
 namespace pf {
-constexpr int D = 128, BM = 128, BN = 64, STAGES = 3;
+constexpr int D = 128, BM = 128, BN = 128, NSLOT = 4;
 constexpr int kQBytes = BM * D * 2;          // one RG's Q tile: 2 halves of [128 x 64]
-constexpr int kKVBytes = BN * D * 2;         // one K (or V) tile: 2 halves of [64 x 64]
-constexpr int kPBytes = BM * BN * 2;         // one RG's P tile [128 x 64]
+constexpr int kTileBytes = BN * D * 2;       // one K (or V) tile: 2 halves of [128 x 64]
 constexpr int kSmemQ = 0;
-constexpr int kSmemK = kSmemQ + 2 * kQBytes;
-constexpr int kSmemV = kSmemK + STAGES * kKVBytes;
-constexpr int kSmemP = kSmemV + STAGES * kKVBytes;
-constexpr int kSmemBar = kSmemP + 4 * kPBytes;  // 2 row groups x 2 P buffers
-constexpr int kNumBars = 1 + 2 * STAGES + 8;
+constexpr int kSmemKV = kSmemQ + 2 * kQBytes;
+constexpr int kSmemBar = kSmemKV + NSLOT * kTileBytes;
+constexpr int kNumBars = 1 + 2 * NSLOT + 6;
 constexpr int kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;
-constexpr int kThreads = 288;
+constexpr int kThreads = 384;  // 2 softmax warpgroups + 1 warpgroup holding the TMA and MMA warps (2 idle warps)
 }  // namespace pf
 
 struct PrefillParams {
@@ -57,31 +50,32 @@ __global__ void __launch_bounds__(pf::kThreads, 1)
 prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const PrefillParams p) {
   using namespace pf;
+  pdl_launch_dependents();
+  pdl_wait();  // q / k / v (and the cache) come from the previous kernel
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t bars = smem_base + kSmemBar;
   const uint32_t q_full = bars;
-  auto kv_full = [&](int s) { return bars + (1 + s) * 8; };
-  auto kv_empty = [&](int s) { return bars + (1 + STAGES + s) * 8; };
-  auto s_full = [&](int g, int b) { return bars + (1 + 2 * STAGES + g * 2 + b) * 8; };      // S buffer b of group g written
-  auto o_full = [&](int g, int b) { return bars + (1 + 2 * STAGES + 4 + g * 2 + b) * 8; };  // PV that read P buffer b retired
+  auto slot_full = [&](int s) { return bars + (1 + s) * 8; };
+  auto slot_empty = [&](int s) { return bars + (1 + NSLOT + s) * 8; };
+  auto s_full = [&](int g) { return bars + (1 + 2 * NSLOT + g) * 8; };       // S_j of group g is in TMEM
+  auto p_ready = [&](int g) { return bars + (1 + 2 * NSLOT + 2 + g) * 8; };  // P_j of group g is in TMEM (128 arrivals)
+  auto o_done = [&](int g) { return bars + (1 + 2 * NSLOT + 4 + g) * 8; };   // PV_j of group g has retired
   const uint32_t tmem_slot = bars + kNumBars * 8;
 
-  pdl_launch_dependents();
-  pdl_wait();  // q / k / v (and the cache) come from the previous kernel
-  const int seq = blockIdx.z, head = blockIdx.y, qblk = blockIdx.x;
+  const int seq = blockIdx.z, head = blockIdx.y;
+  const int qblk = gridDim.x - 1 - blockIdx.x;  // longest (latest rows) first: shorter tail
   const int kvh = head / (p.H / p.Hkv);
   const int q0 = __ldg(p.cu_q + seq), Lq = __ldg(p.cu_q + seq + 1) - q0;
   const int k0 = __ldg(p.cu_k + seq), Lk = __ldg(p.cu_k + seq + 1) - k0;
   if (qblk * 2 * BM >= Lq) return;  // uniform per CTA: nothing allocated yet
   const int shift = Lk - Lq;        // bottom-right alignment
-  // number of KV tiles each row group needs (0 when the group has no valid row)
-  auto tiles_for = [&](int g) {
+  auto tiles_for = [&](int g) {     // number of KV tiles a row group needs (0 when it has no valid row)
     const int first = qblk * 2 * BM + g * BM;
     if (first >= Lq) return 0;
     const int last = min(first + BM, Lq) - 1;
-    const int visible = max(1, min(Lk, shift + last + 1));  // keys the group's last row sees
+    const int visible = max(1, min(Lk, shift + last + 1));
     return (visible + BN - 1) / BN;
   };
   const int n_rg[2] = {tiles_for(0), tiles_for(1)};
@@ -91,9 +85,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k); tma_prefetch_desc(&tmap_v);
     mbar_init(q_full, 1);
-    for (int s = 0; s < STAGES; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 2); }
-    for (int g = 0; g < 2; ++g)
-      for (int b = 0; b < 2; ++b) { mbar_init(s_full(g, b), 1); mbar_init(o_full(g, b), 1); }
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(slot_full(s), 1); mbar_init(slot_empty(s), 1); }
+    for (int g = 0; g < 2; ++g) { mbar_init(s_full(g), 1); mbar_init(p_ready(g), BM); mbar_init(o_done(g), 1); }
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc<512>(tmem_slot);
@@ -102,7 +95,14 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<uint32_t*>(smem_gen + kSmemBar + kNumBars * 8);
 
-  if (warp == 8) {
+  // Register reallocation (setmaxnreg, per warpgroup): the producer / MMA warpgroup keeps 88 registers per thread and
+  // donates the rest; each softmax thread holds a full 128-key S row (128 registers) and gets 208.
+  if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");  // must dominate the role code below (and only it)
+  }
+  if (warp >= 10) {
+    // idle warps of the third warpgroup
+  } else if (warp == 8) {
     if (lane == 0) {
       // ===== TMA producer =====
       mbar_expect_tx(q_full, 2 * kQBytes);
@@ -111,63 +111,92 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           tma_load_2d(smem_base + kSmemQ + g * kQBytes + hf * (BM * 128), &tmap_q, q_full, head * D + hf * 64,
                       q0 + qblk * 2 * BM + g * BM);
       const int32_t* table = p.tables ? p.tables + static_cast<int64_t>(seq) * p.max_blocks : nullptr;
-      for (int j = 0; j < n_cta; ++j) {
-        const int st = j % STAGES;
-        mbar_wait(kv_empty(st), ((j / STAGES) & 1) ^ 1);
-        mbar_expect_tx(kv_full(st), 2 * kKVBytes);
-        const uint32_t dk = smem_base + kSmemK + st * kKVBytes, dv = smem_base + kSmemV + st * kKVBytes;
+      for (int t = 0; t < 2 * n_cta; ++t) {  // t even: K_{t/2}, t odd: V_{t/2}
+        const int j = t >> 1, slot = t % NSLOT;
+        const CUtensorMap* map = (t & 1) ? &tmap_v : &tmap_k;
+        mbar_wait(slot_empty(slot), ((t / NSLOT) & 1) ^ 1);
+        mbar_expect_tx(slot_full(slot), kTileBytes);
+        const uint32_t dst = smem_base + kSmemKV + slot * kTileBytes;
         if (table == nullptr) {
-          for (int hf = 0; hf < 2; ++hf) {
-            tma_load_2d(dk + hf * (BN * 128), &tmap_k, kv_full(st), kvh * D + hf * 64, k0 + j * BN);
-            tma_load_2d(dv + hf * (BN * 128), &tmap_v, kv_full(st), kvh * D + hf * 64, k0 + j * BN);
-          }
+          for (int hf = 0; hf < 2; ++hf)
+            tma_load_2d(dst + hf * (BN * 128), map, slot_full(slot), kvh * D + hf * 64, k0 + j * BN);
         } else {
-          for (int c = 0; c < BN / p.box_tok; ++c) {  // box_tok = min(64, block_size) tokens per TMA box
+          for (int c = 0; c < BN / p.box_tok; ++c) {  // box_tok = min(128, block_size) tokens per TMA box
             const int tok = j * BN + c * p.box_tok;
             const int bi = tok / p.block_size;
-            int blk = bi < p.max_blocks ? __ldg(table + bi) : -1;
-            // a block id < 0 (only past the sequence end) is redirected far out of bounds: TMA zero-fills
-            const int blk_c = blk < 0 ? 0x3fffff : blk;
-            for (int hf = 0; hf < 2; ++hf) {
-              const uint32_t off = hf * (BN * 128) + c * p.box_tok * 128;
-              tma_load_4d(dk + off, &tmap_k, kv_full(st), hf * 64, tok - bi * p.block_size, kvh, blk_c);
-              tma_load_4d(dv + off, &tmap_v, kv_full(st), hf * 64, tok - bi * p.block_size, kvh, blk_c);
-            }
+            const int blk = bi < p.max_blocks ? __ldg(table + bi) : -1;
+            const int blk_c = blk < 0 ? 0x3fffff : blk;  // past the sequence end: far out of bounds -> TMA zero-fills
+            for (int hf = 0; hf < 2; ++hf)
+              tma_load_4d(dst + hf * (BN * 128) + c * p.box_tok * 128, map, slot_full(slot), hf * 64,
+                          tok - bi * p.block_size, kvh, blk_c);
           }
         }
       }
     }
+  } else if (warp == 9) {
+    if (lane == 0) {
+      // ===== MMA issuer (both row groups) =====
+      constexpr uint32_t idesc_s = umma_idesc_bf16(BM, BN, 0, 0);  // Q K-major, K K-major
+      constexpr uint32_t idesc_o = umma_idesc_bf16(BM, D, 0, 1);   // P K-major (TMEM), V MN-major
+      auto tile_full = [&](int t) { mbar_wait(slot_full(t % NSLOT), (t / NSLOT) & 1); tc_fence_after(); };
+      auto issue_s = [&](int g, int j) {  // S_j^g = Q^g . K_j^T
+        const uint32_t sQ = smem_base + kSmemQ + g * kQBytes;
+        const uint32_t sK = smem_base + kSmemKV + ((2 * j) % NSLOT) * kTileBytes;
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+          const uint64_t ad = umma_desc_sw128(sQ + (ks >> 2) * (BM * 128) + (ks & 3) * 32, 16, 1024);
+          const uint64_t bd = umma_desc_sw128(sK + (ks >> 2) * (BN * 128) + (ks & 3) * 32, 16, 1024);
+          umma_bf16_ss(tmem_base + g * 256, ad, bd, idesc_s, ks != 0);
+        }
+        umma_commit(s_full(g));
+      };
+      mbar_wait(q_full, 0);
+      if (n_cta > 0) {
+        tile_full(0);
+        for (int g = 0; g < 2; ++g)
+          if (n_rg[g] > 0) issue_s(g, 0);
+        umma_commit(slot_empty(0));  // K_0 consumed once these MMAs retire
+      }
+      for (int j = 0; j < n_cta; ++j) {
+        bool v_waited = false, k_waited = false;
+        for (int g = 0; g < 2; ++g) {
+          if (j >= n_rg[g]) continue;
+          mbar_wait(p_ready(g), j & 1);  // softmax of group g wrote P_j (and rescaled O if it had to)
+          tc_fence_after();
+          if (!v_waited) { tile_full(2 * j + 1); v_waited = true; }
+          const uint32_t sV = smem_base + kSmemKV + ((2 * j + 1) % NSLOT) * kTileBytes;
+#pragma unroll
+          for (int ks = 0; ks < BN / 16; ++ks) {
+            // P: 16 keys = 8 packed columns per step.  V tile: rows = keys, 64 contiguous d per row; the two d halves
+            // (MN groups) are 16 KiB apart, 8 keys per 1 KiB.
+            const uint64_t bd = umma_desc_sw128(sV + ks * 2048, BN * 128, 1024);
+            umma_bf16_ts(tmem_base + g * 256 + 128, tmem_base + g * 256 + ks * 8, bd, idesc_o, (j | ks) != 0);
+          }
+          umma_commit(o_done(g));
+          if (j + 1 < n_rg[g]) {
+            if (!k_waited) { tile_full(2 * j + 2); k_waited = true; }
+            issue_s(g, j + 1);  // executes after PV_j^g in the pipe: P_j (aliased with S) is no longer needed by then
+          }
+        }
+        // both groups' uses of V_j and K_{j+1} are issued: release the slots once they retire
+        umma_commit(slot_empty((2 * j + 1) % NSLOT));
+        if (j + 1 < n_cta) umma_commit(slot_empty((2 * j + 2) % NSLOT));
+      }
+    }
   } else {
-    // ===== row groups: MMA issue (thread 0 of the group) + softmax + output =====
+    // ===== row groups: softmax + output =====
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;\n");
     const int g = warp >> 2;               // row group 0 / 1
     const int t = threadIdx.x & 127;       // row within the group's tile == TMEM lane
     const int n_my = n_rg[g];
-    const bool issuer = t == 0;
     const int row = qblk * 2 * BM + g * BM + t;  // row within the sequence's queries
     const int limit = shift + row;               // last visible key index
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t tS_mma = tmem_base + g * 256, tO_mma = tS_mma + 128;   // S buffers at +0 / +64, O at +128
-    const uint32_t tO = tO_mma + lane_off;
-    const uint32_t sQ = smem_base + kSmemQ + g * kQBytes;
-    constexpr uint32_t idesc_s = umma_idesc_bf16(BM, BN, 0, 0);   // Q K-major, K K-major
-    constexpr uint32_t idesc_o = umma_idesc_bf16(BM, D, 0, 1);    // P K-major, V MN-major
-    constexpr float kRescaleThreshold = 8.0f;                     // log2 units: P stays <= 2^8 between refreshes
-
-    auto issue_s = [&](int j) {  // S_j = Q . K_j^T into S buffer j & 1
-      const int st = j % STAGES;
-      mbar_wait(kv_full(st), (j / STAGES) & 1);
-      tc_fence_after();
-      const uint32_t sK = smem_base + kSmemK + st * kKVBytes;
-#pragma unroll
-      for (int ks = 0; ks < D / 16; ++ks) {
-        const uint64_t ad = umma_desc_sw128(sQ + (ks >> 2) * (BM * 128) + (ks & 3) * 32, 16, 1024);
-        const uint64_t bd = umma_desc_sw128(sK + (ks >> 2) * (BN * 128) + (ks & 3) * 32, 16, 1024);
-        umma_bf16_ss(tS_mma + (j & 1) * BN, ad, bd, idesc_s, ks != 0);
-      }
-      umma_commit(s_full(g, j & 1));
-    };
-    // 2^x for x <= 0 on the FMA pipe: x = n + f, f in [0, 1); 2^f by a degree-3 minimax polynomial (rel. err 1e-4, far
-    // below bf16's 2^-9), 2^n by adding n to the exponent field.
+    const uint32_t tS = tmem_base + g * 256 + lane_off;  // S (fp32, 128 columns) / P (packed bf16, first 64 columns)
+    const uint32_t tO = tS + 128;
+    constexpr float kRescaleThreshold = 8.0f;  // log2 units: P stays <= 2^8 between refreshes
+    // 2^x for x <= 0 on the FMA pipe: x = n + f, f in [0, 1); 2^f by a degree-3 polynomial (rel. err 2.3e-4, far below
+    // bf16's 2^-9), 2^n by adding n to the exponent field.
     auto exp2_poly = [](float x) {
       x = fmaxf(x, -126.f);
       const float n = floorf(x);
@@ -179,35 +208,25 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
     };
 
     float m_ref = -INFINITY, l_run = 0.f;  // m_ref: the (stale-by-design) maximum the exponentials are taken against
-    if (issuer && n_my > 0) {
-      mbar_wait(q_full, 0);
-      issue_s(0);
-    }
     for (int j = 0; j < n_my; ++j) {
-      const int st = j % STAGES, b = j & 1;
-      const uint32_t sP = smem_base + kSmemP + (g * 2 + b) * kPBytes;
-      uint8_t* sP_gen = smem_gen + kSmemP + (g * 2 + b) * kPBytes;
-      mbar_wait(s_full(g, b), (j >> 1) & 1);     // S_j is in TMEM
-      // S_{j+1} goes to the other S buffer (its previous content, S_{j-1}, was consumed before the last bar.sync):
-      // the tensor core computes it while this group works on tile j.
-      if (issuer && j + 1 < n_my) issue_s(j + 1);
+      mbar_wait(s_full(g), j & 1);
+      // S_j was issued after PV_{j-1} and MMAs of one thread retire in order: this wait is free.  It consumes the o_done
+      // phases strictly in order (a parity wait may never lag two phases behind), and O is quiescent from here on.
+      if (j > 0) mbar_wait(o_done(g), (j - 1) & 1);
       tc_fence_after();
-      // ---- softmax on S_j ---------------------------------------------------------------------
-      uint32_t sr[2][32];
-      const uint32_t tS = tS_mma + b * BN + lane_off;
-      tmem_ld_32x32b_x32(tS, sr[0]);
-      tmem_ld_32x32b_x32(tS + 32, sr[1]);
+      uint32_t sr[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sr[c]);
       tmem_ld_wait();
       const int kbase = j * BN;
-      const bool need_mask = (kbase + BN - 1 > limit) || (kbase + BN > Lk);
-      if (need_mask) {
+      if ((kbase + BN - 1 > limit) || (kbase + BN > Lk)) {
 #pragma unroll
-        for (int c = 0; c < 64; ++c)
+        for (int c = 0; c < BN; ++c)
           if (kbase + c > limit || kbase + c >= Lk) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
       }
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // 4 independent chains
 #pragma unroll
-      for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
+      for (int c = 0; c < BN; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       // lazy rescale: refresh the reference maximum only when this tile exceeds it by more than the threshold
       const bool refresh = (mx - m_ref) * p.scale_log2 > kRescaleThreshold;  // also true for the first finite tile
@@ -218,8 +237,6 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         l_run *= corr;
       }
       if (j > 0 && __any_sync(0xffffffffu, refresh)) {  // tcgen05.ld/st are warp-collective: the whole warp takes part
-        mbar_wait(o_full(g, (j - 1) & 1), ((j - 1) >> 1) & 1);  // PV_{j-1} retired: O is quiescent
-        tc_fence_after();
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) {
           uint32_t orr[32];
@@ -229,50 +246,32 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           for (int e = 0; e < 32; ++e) orr[e] = __float_as_uint(__uint_as_float(orr[e]) * corr);
           tmem_st_32x32b_x32(tO + c * 32, orr);
         }
-        tmem_st_wait();
       }
-      if (j >= 2) mbar_wait(o_full(g, b), ((j - 2) >> 1) & 1);  // PV_{j-2} retired: P buffer b may be rewritten
       const float moff = (m_ref == -INFINITY) ? 0.f : m_ref * p.scale_log2;
       float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int c8 = 0; c8 < 8; ++c8) {  // 8 chunks of 8 keys = 16 bytes of bf16 P each
-        uint32_t pk[4];
+      for (int h2 = 0; h2 < 2; ++h2) {  // 2 x 64 keys -> 2 x 32 packed columns
+        uint32_t pk[32];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int c = c8 * 8 + e * 2;
+        for (int e = 0; e < 32; ++e) {
+          const int c = h2 * 64 + e * 2;
           const float a0 = fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff);
           const float a1 = fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff);
           const float p0 = fast_exp2(a0);   // MUFU
           const float p1 = exp2_poly(a1);   // FMA pipe
-          ls4[e] += p0 + p1;
-          pk[e] = pack_bf16x2(p0, p1);
+          ls4[e & 3] += p0 + p1;
+          pk[e] = pack_bf16x2(p0, p1);      // low half = even key: consecutive K elements share a 32-bit column
         }
-        // SWIZZLE_128B K-major: row t at t*128 bytes, 16-byte chunk index XOR (row & 7)
-        *reinterpret_cast<uint4*>(sP_gen + t * 128 + ((c8 ^ (t & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        tmem_st_32x32b_x32(tS + h2 * 32, pk);  // P over this thread's own S lane
       }
       l_run += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
+      tmem_st_wait();
       tc_fence_before();
-      fence_proxy_async();  // generic-proxy writes of P -> visible to the tensor core (async proxy)
-      asm volatile("bar.sync %0, 128;\n" ::"r"(1 + g) : "memory");
-      // ---- O += P_j . V_j ------------------------------------------------------------------------
-      if (issuer) {
-        tc_fence_after();
-        const uint32_t sV = smem_base + kSmemV + st * kKVBytes;
-#pragma unroll
-        for (int ks = 0; ks < BN / 16; ++ks) {
-          const uint64_t ad = umma_desc_sw128(sP + ks * 32, 16, 1024);
-          // V tile: rows = keys (k), 64 contiguous d per row; 2 MN groups (d halves) 8 KiB apart, 8 keys per 1 KiB
-          const uint64_t bd = umma_desc_sw128(sV + ks * 2048, BN * 128, 1024);
-          umma_bf16_ss(tO_mma, ad, bd, idesc_o, (j | ks) != 0);
-        }
-        umma_commit(o_full(g, b));
-        umma_commit(kv_empty(st));
-      }
+      mbar_arrive(p_ready(g));
     }
     float acc[D];
     if (n_my > 0) {
-      if (n_my >= 2) mbar_wait(o_full(g, (n_my - 2) & 1), ((n_my - 2) >> 1) & 1);
-      mbar_wait(o_full(g, (n_my - 1) & 1), ((n_my - 1) >> 1) & 1);
+      mbar_wait(o_done(g), (n_my - 1) & 1);
       tc_fence_after();
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
@@ -283,14 +282,6 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
         for (int e = 0; e < 32; ++e) acc[c * 32 + e] = __uint_as_float(orr[e]);
       }
       tc_fence_before();
-    }
-    // tiles this group does not need still have to be released for the other group / the producer
-    if (issuer) {
-      for (int j = n_my; j < n_cta; ++j) {
-        const int st = j % STAGES;
-        mbar_wait(kv_full(st), (j / STAGES) & 1);
-        mbar_arrive(kv_empty(st));
-      }
     }
     // ---- output -------------------------------------------------------------------------------------
     if (n_my > 0 && row < Lq) {
