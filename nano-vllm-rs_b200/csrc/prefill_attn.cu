@@ -10,7 +10,7 @@
 //                       32 KiB slots; dense K/V via a 2-D map, paged K/V via a 4-D map (d, token, head, block) + block_tables
 //   warp 9 (one lane)   MMA issuer for both groups: S = Q . K^T (8 x tcgen05.mma M128 N128 K16, both operands K-major in
 //                       shared memory) and O += P . V (8 x tcgen05.mma with A = P read from TENSOR MEMORY, V MN-major)
-//   RG threads          tcgen05.ld S row -> row max -> exp2 (half on MUFU, half by a polynomial on the FMA pipe) ->
+//   RG threads          tcgen05.ld S row -> row max -> exp2 (3/4 on MUFU, 1/4 by a polynomial on the FMA pipe) ->
 //                       P as packed bf16 written BACK INTO TMEM over the S columns (tcgen05.st; each thread only touches its
 //                       own lane, so no cross-thread hazard) -> mbarrier arrive.  No shared-memory round trip for P.
 //                       O accumulates in TMEM across tiles; the reference maximum is refreshed lazily (only when a tile
@@ -257,8 +257,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const int c = h2 * 64 + e * 2;
           const float a0 = fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff);
           const float a1 = fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff);
-          const float p0 = fast_exp2(a0);   // MUFU
-          const float p1 = exp2_poly(a1);   // FMA pipe
+          const float p0 = fast_exp2(a0);                               // MUFU
+          const float p1 = (e & 1) ? exp2_poly(a1) : fast_exp2(a1);     // every 4th element on the FMA pipe
           ls4[e & 3] += p0 + p1;
           pk[e] = pack_bf16x2(p0, p1);      // low half = even key: consecutive K elements share a 32-bit column
         }
