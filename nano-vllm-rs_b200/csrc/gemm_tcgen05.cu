@@ -61,7 +61,10 @@ __device__ __forceinline__ void store_row32<float>(float* dst, const uint32_t (&
 
 // SILU == true: w = [gate (N rows) | up (N rows)]; the B tile is staged as BN/2 gate rows + the matching BN/2 up rows and
 // the epilogue writes y[:, n_tile*BN/2 + c] = silu(gate) * up (see gemm_tcgen05_2cta.cu for the CTA-pair variant).
-template <int BN, typename OutT, bool SILU>
+// CN > 1: clusters of CN CTAs along N work on the same 128-row x tile.  Each CTA loads 128/CN rows of it and MULTICASTS
+// them into all CN shared memories (L2 -> SM traffic for x drops by CN: the bound for small-N, long-K shards such as the
+// TP=8 qkv / o / down projections); a stage is released only when all CN CTAs' MMAs have retired (multicast commit).
+template <int BN, typename OutT, bool SILU, int CN>
 __global__ void __launch_bounds__(256, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles) {
@@ -82,6 +85,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = K / C::BK;
+  // num_tiles counts CLUSTER tiles: (m_tile, group of CN consecutive n-tiles); this CTA owns n-tile group*CN + rank
+  const int rank = CN > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+  const int cta0 = static_cast<int>(blockIdx.x) / CN, cta_stride = static_cast<int>(gridDim.x) / CN;
+  constexpr uint16_t kMask = static_cast<uint16_t>((1u << CN) - 1u);
   pdl_launch_dependents();  // everything up to pdl_wait() below is independent of the previous kernel
 
   if (warp == 0 && lane == 0) {
@@ -91,7 +98,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 1);
+      mbar_init(empty_bar(s), CN);  // every CTA of the cluster must have drained the stage before it is refilled
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
@@ -101,7 +108,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   }
   if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CN > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -117,9 +124,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
       }
     };
+    auto load_x = [&](int stage, int kb, int m_tile) {
+      if constexpr (CN > 1) {
+        constexpr int kRows = C::BM / CN;  // this CTA's share of the x tile, multicast to the whole cluster
+        tma_load_2d_mcast(sA + stage * C::kABytes + rank * kRows * 128, &tmap_x, full_bar(stage), kb * C::BK,
+                          m_tile * C::BM + rank * kRows, kMask);
+      } else {
+        tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
+      }
+    };
     const int pre = num_kb < STAGES ? num_kb : STAGES;
     {
-      const int n_tile0 = blockIdx.x / num_m_tiles;
+      const int n_tile0 = (cta0 / num_m_tiles) * CN + rank;
       for (int kb = 0; kb < pre; ++kb) {
         mbar_expect_tx(full_bar(kb), C::kStageBytes);
         load_w(kb, kb, n_tile0);
@@ -129,15 +145,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     int stage = 0;
     uint32_t phase = 0;
     bool first = true;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
+    for (int tile = cta0; tile < num_tiles; tile += cta_stride) {
+      const int m_tile = tile % num_m_tiles, n_tile = (tile / num_m_tiles) * CN + rank;
       for (int kb = 0; kb < num_kb; ++kb) {
         if (first && kb < pre) {  // w tile already in flight, barrier already armed
-          tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
+          load_x(stage, kb, m_tile);
         } else {
           mbar_wait(empty_bar(stage), phase ^ 1);
           mbar_expect_tx(full_bar(stage), C::kStageBytes);
-          tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), kb * C::BK, m_tile * C::BM);
+          load_x(stage, kb, m_tile);
           load_w(stage, kb, n_tile);
         }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -149,7 +165,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     constexpr uint32_t idesc = umma_idesc_bf16(C::BM, BN, 0, 0);
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = cta0; tile < num_tiles; tile += cta_stride) {
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);  // epilogue has drained this TMEM buffer
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
@@ -163,7 +179,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           const uint64_t bdesc = umma_desc_sw128(b0 + k * 32, 16, 1024);
           umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
         }
-        umma_commit(empty_bar(stage));                      // smem stage reusable once these MMAs retire
+        if constexpr (CN > 1) umma_commit_mcast(empty_bar(stage), kMask);  // tell every producer of the cluster
+        else umma_commit(empty_bar(stage));                 // smem stage reusable once these MMAs retire
         if (kb == num_kb - 1) umma_commit(tfull_bar(acc));  // accumulator complete
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -175,8 +192,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     const int q = warp & 3;  // TMEM lane quadrant this warp may access
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
+    for (int tile = cta0; tile < num_tiles; tile += cta_stride) {
+      const int m_tile = tile % num_m_tiles, n_tile = (tile / num_m_tiles) * CN + rank;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const int row = m_tile * C::BM + q * 32 + lane;
@@ -217,18 +234,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CN > 1) cluster_sync_all(); else __syncthreads();  // peers may still multicast into / signal this CTA
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<C::kTmemCols>(tmem_base);
   }
 }
 
-template <int BN, typename OutT, bool SILU = false>
+template <int BN, typename OutT, bool SILU = false, int CN = 1>
 static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy,
                        cudaStream_t st) {
   using C = GemmCfg<BN>;
-  auto kern = gemm_tcgen05_kernel<BN, OutT, SILU>;
+  auto kern = gemm_tcgen05_kernel<BN, OutT, SILU, CN>;
   static bool attr_set = false;
   if (!attr_set) {
     NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -236,10 +253,27 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
   }
   const int num_m_tiles = (M + C::BM - 1) / C::BM;
   const int num_n_tiles = SILU ? (N + BN / 2 - 1) / (BN / 2) : (N + BN - 1) / BN;
-  const int num_tiles = num_m_tiles * num_n_tiles;
-  const int grid = num_tiles < sm_count() ? num_tiles : sm_count();
-  NVLLM_CUDA(launch_pdl(kern, dim3(grid), dim3(256), C::kSmemBytes, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
-                        num_m_tiles, num_tiles));
+  const int num_tiles = num_m_tiles * (num_n_tiles / CN);  // cluster tiles (the caller guarantees num_n_tiles % CN == 0)
+  const int max_clusters = sm_count() / CN;
+  const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+  if constexpr (CN == 1) {
+    NVLLM_CUDA(launch_pdl(kern, dim3(clusters), dim3(256), C::kSmemBytes, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
+                          num_m_tiles, num_tiles));
+  } else {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(clusters * CN);
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CN; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles));
+  }
   return 0;
 }
 
@@ -282,6 +316,15 @@ static bool want_2cta(int m, int n, int k) {
   return true;
 }
 
+static bool use_mcast() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("NVLLM_GEMM_MCAST");  // A/B knob: 0 disables the x-multicast clusters
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 static bool use_2cta() {
   static int v = -1;
   if (v < 0) {
@@ -310,10 +353,18 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   if (want_2cta(m, n, k))
     return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, static_cast<cudaStream_t>(stream));
   const int bn = pick_bn(m, n);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
   CUtensorMap tx, tw;
+  // x-multicast clusters of 4 along N: worth it when x (re-read once per n-tile) dominates the L2 -> SM traffic,
+  // i.e. several n-tiles of a narrow width and a long K.
+  if (use_mcast() && bn <= 64 && n % (4 * bn) == 0 && k >= 2048 && out_dtype == NVLLM_BF16) {
+    if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 32)) return rc;
+    if (int rc = make_tmap_bf16_2d(&tw, w, n, k, ldw, bn)) return rc;
+    return bn == 64 ? launch_gemm<64, bf16, false, 4>(tx, tw, y, m, n, k, ldy, st)
+                    : launch_gemm<32, bf16, false, 4>(tx, tw, y, m, n, k, ldy, st);
+  }
   if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
   if (int rc = make_tmap_bf16_2d(&tw, w, n, k, ldw, bn)) return rc;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
 #define NVLLM_GEMM_CASE(BNV)                                                                     \
   case BNV:                                                                                      \
     return out_dtype == NVLLM_BF16 ? launch_gemm<BNV, bf16>(tx, tw, y, m, n, k, ldy, st)         \

@@ -71,6 +71,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap
       "l"(m), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// 2-D tile load multicast to every CTA of `cta_mask` in the cluster: the tile lands at the same shared-memory offset in
+// each of them and each destination's mbarrier (same offset) receives the transaction bytes.
+__device__ __forceinline__ void tma_load_2d_mcast(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c0, int c1,
+                                                  uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;\n" ::"r"(smem_dst),
+      "l"(m), "r"(bar), "r"(c0), "r"(c1), "h"(cta_mask)
+      : "memory");
+}
 // 4-D tile load (paged KV: d, head, token-in-block, block).
 __device__ __forceinline__ void tma_load_4d(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar,
                                             int c0, int c1, int c2, int c3) {
@@ -191,6 +200,12 @@ __device__ __forceinline__ void umma_bf16_ss_cg2(uint32_t tmem_d, uint64_t adesc
       "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}\n" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(z)
       : "memory");
+}
+// cta_group::1 commit that arrives on the barrier at this offset in every CTA of `cta_mask` (multicast-operand rings).
+__device__ __forceinline__ void umma_commit_mcast(uint32_t bar, uint16_t cta_mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(bar),
+               "h"(cta_mask)
+               : "memory");
 }
 // Arrives on the barrier at this offset in every CTA of `cta_mask` once the issued cta_group::2 MMAs have completed.
 __device__ __forceinline__ void umma_commit_cg2(uint32_t bar, uint16_t cta_mask) {

@@ -16,6 +16,7 @@ ATOL, RTOL = 2e-2, 2 ** -7
 SHAPES = [
     (128, 128, 64), (1, 8, 64), (5, 40, 128), (129, 136, 192), (256, 4096, 1024), (300, 1024, 2048),
     (256, 6144, 1024), (64, 1024, 3072), (7, 264, 4096), (512, 512, 512),
+    (512, 768, 4096), (256, 1024, 3072), (130, 256, 2048),   # x-multicast clusters (narrow N, long K: TP shards)
 ]
 
 
