@@ -14,6 +14,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _tp_worker(rank, world, port, arch, prompts, max_tokens, q):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    import time
+    t_start = time.time()
+    say = lambda msg: print(f"[tp rank {rank}/{world} +{time.time() - t_start:5.1f}s] {msg}", flush=True)
     try:
         import torch.distributed as dist
         from nano_vllm_rs_b200 import _ffi
@@ -28,10 +31,13 @@ def _tp_worker(rank, world, port, arch, prompts, max_tokens, q):
             uid.copy_(torch.tensor(list(buf), dtype=torch.uint8))
         dist.broadcast(uid, 0)
         h = E.vp()
+        say("process group up")
         _ffi.check(lib.nvllm_comm_init(E.C.byref(h), bytes(uid.cpu().tolist()), rank, world))
+        say("nvllm communicator up")
         cfg = E.Config(arch, kvcache_block_size=16, num_kvcache_blocks=64, tensor_parallel_size=world, tp_rank=rank)
         sched, runner = E.Scheduler(cfg), E.ModelRunner(cfg, comm=h)
         runner.init_weights(1234, 0.05)
+        say("runner ready")
         for p in prompts:
             sched.add_sequence(p, E.SamplingParams(temperature=0.0, max_tokens=max_tokens, ignore_eos=True))
         trace = []
@@ -40,6 +46,7 @@ def _tp_worker(rank, world, port, arch, prompts, max_tokens, q):
             toks, logits = runner.execute_model(b, return_logits=True)
             trace.append((toks.copy(), logits.copy()))
             sched.postprocess(toks)
+        say(f"{len(trace)} steps done")
         q.put((rank, "ok", trace))
         dist.barrier()
         _ffi.check(lib.nvllm_comm_destroy(h))
