@@ -136,6 +136,16 @@ int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n,
 int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_gate_up, int32_t m, int32_t inter, int32_t k,
                              int64_t ldx, int64_t ldw, int64_t ldout, void* workspace, size_t workspace_bytes,
                              void* stream);
+/* QKVParallelLinear::forward (linear.rs:354-356) + the q/k norm, RotaryEmbedding::forward and Attention::store_kv_cache
+ * that follow it (qwen3.rs:219-229, attention.rs:150-174) in ONE kernel: qkv[M, (H+2Hkv)*128] = x . Wqkv^T, each 128-wide
+ * output tile being one head whose epilogue thread applies the same math (and rounding points) as
+ * nvllm_qknorm_rope_store before writing the qkv row and, for k / v heads, the paged cache.  head_dim 128 only.
+ * k_cache may be NULL (no store).  Equivalent to nvllm_gemm_bf16 + nvllm_qknorm_rope_store. */
+int nvllm_gemm_qkv_rope_store(void* qkv, const void* x, const void* w_qkv, int32_t m, int32_t k, int64_t ldx, int64_t ldw,
+                              const int64_t* positions, const float* cos_sin, const void* q_norm_w,
+                              const void* k_norm_w, float eps, int32_t num_heads, int32_t num_kv_heads,
+                              int32_t head_dim, int32_t max_position, void* k_cache, void* v_cache,
+                              const int32_t* slot_mapping, const nvllm_kv_layout* layout, void* stream);
 /* Plain CUDA-core version of the same contract; test infrastructure for the kernel above (used to
  * check large shapes on the device where the CPU oracle is too slow).  Never on the product path. */
 int nvllm_gemm_bf16_simt(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,

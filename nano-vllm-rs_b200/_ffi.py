@@ -47,6 +47,7 @@ PROTOTYPES = {
     "nvllm_gemm_workspace_bytes": (sz, [i32, i32, i32]),
     "nvllm_gemm_bf16": (i32, [vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, vp, sz, vp]),
     "nvllm_gemm_silu_mul_bf16": (i32, [vp, vp, vp, i32, i32, i32, i64, i64, i64, vp, sz, vp]),
+    "nvllm_gemm_qkv_rope_store": (i32, [vp, vp, vp, i32, i32, i64, i64, vp, vp, vp, vp, f32, i32, i32, i32, i32, vp, vp, vp, LP, vp]),
     "nvllm_gemm_bf16_simt": (i32, [vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, vp]),
     "nvllm_add_rmsnorm": (i32, [vp, vp, vp, vp, i32, i32, f32, i32, vp]),
     "nvllm_qknorm_rope_store": (i32, [vp, vp, vp, vp, vp, f32, i32, i32, i32, i32, i32, vp, vp, vp, LP, i32, vp]),

@@ -61,13 +61,32 @@ __device__ __forceinline__ void store_row32<float>(float* dst, const uint32_t (&
 
 // SILU == true: w = [gate (N rows) | up (N rows)]; the B tile is staged as BN/2 gate rows + the matching BN/2 up rows and
 // the epilogue writes y[:, n_tile*BN/2 + c] = silu(gate) * up (see gemm_tcgen05_2cta.cu for the CTA-pair variant).
+// Optional qkv epilogue (ROPE mode, BN == 128 == head_dim): each output tile is one head of the packed [q | k | v] row,
+// and each epilogue thread owns that head for one token.  It applies what Qwen3Attention::forward does between qkv_proj
+// and Attention::forward (qwen3.rs:219-229) plus Attention::store_kv_cache (attention.rs:150-174): round to bf16 (the
+// qkv tensor), per-head RMSNorm (q/k), bf16, half-split RoPE from the f32 table, bf16; q/k/v rows go to the qkv buffer
+// and k/v additionally into the paged cache at slot_mapping[token] — same rounding points as the stand-alone kernel.
+struct RopeEpi {
+  const int64_t* positions;
+  const float* cos_sin;     // [max_position, 128]
+  const bf16* q_norm_w;     // may be NULL (no qk-norm)
+  const bf16* k_norm_w;
+  bf16* k_cache;
+  bf16* v_cache;
+  const int32_t* slot_mapping;
+  int H, Hkv, max_position, block_size;
+  int64_t blk_stride, tok_stride, head_stride;
+  float eps;
+};
+
 // CN > 1: clusters of CN CTAs along N work on the same 128-row x tile.  Each CTA loads 128/CN rows of it and MULTICASTS
 // them into all CN shared memories (L2 -> SM traffic for x drops by CN: the bound for small-N, long-K shards such as the
 // TP=8 qkv / o / down projections); a stage is released only when all CN CTAs' MMAs have retired (multicast commit).
-template <int BN, typename OutT, bool SILU, int CN>
+template <int BN, typename OutT, bool SILU, int CN, bool ROPE = false>
 __global__ void __launch_bounds__(256, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                    OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles) {
+                    OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles,
+                    const RopeEpi re = RopeEpi{}) {
   using C = GemmCfg<BN>;
   constexpr int STAGES = C::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -198,7 +217,68 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       tc_fence_after();
       const int row = m_tile * C::BM + q * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
-      if constexpr (SILU) {
+      if constexpr (ROPE) {
+        static_assert(!ROPE || (BN == 128 && sizeof(OutT) == 2), "ROPE epilogue: one 128-wide head per tile, bf16 out");
+        float v[128];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[c * 32 + e] = __bfloat162float(__float2bfloat16_rn(__uint_as_float(r[e])));  // bf16 qkv
+        }
+        if (row < M) {
+          const int head = n_tile;  // packed row: H q heads, Hkv k heads, Hkv v heads
+          const int kind = head < re.H ? 0 : (head < re.H + re.Hkv ? 1 : 2);
+          if (kind < 2) {
+            const bf16* w = kind == 0 ? re.q_norm_w : re.k_norm_w;
+            if (w != nullptr) {
+              float ss = 0.f;
+#pragma unroll
+              for (int e = 0; e < 128; ++e) ss += v[e] * v[e];
+              const float inv = 1.0f / sqrtf(ss * (1.0f / 128.0f) + re.eps);
+#pragma unroll
+              for (int e = 0; e < 128; ++e) v[e] = __bfloat162float(__float2bfloat16_rn(v[e] * inv * __bfloat162float(w[e])));
+            }
+            int64_t pos = re.positions[row];
+            pos = pos < 0 ? 0 : (pos >= re.max_position ? re.max_position - 1 : pos);
+            const float4* cs = reinterpret_cast<const float4*>(re.cos_sin + pos * 128);
+#pragma unroll
+            for (int e4 = 0; e4 < 16; ++e4) {
+              const float4 c4 = __ldg(cs + e4), s4 = __ldg(cs + 16 + e4);
+              const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, sn[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int e = e4 * 4 + i;
+                const float x1 = v[e], x2 = v[64 + e];
+                v[e] = x1 * cc[i] - x2 * sn[i];
+                v[64 + e] = x2 * cc[i] + x1 * sn[i];
+              }
+            }
+          }
+          uint4 o[16];
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            o[c].x = pack_bf16x2(v[c * 8 + 0], v[c * 8 + 1]); o[c].y = pack_bf16x2(v[c * 8 + 2], v[c * 8 + 3]);
+            o[c].z = pack_bf16x2(v[c * 8 + 4], v[c * 8 + 5]); o[c].w = pack_bf16x2(v[c * 8 + 6], v[c * 8 + 7]);
+          }
+          uint4* dst = reinterpret_cast<uint4*>(y + row * ldy + head * 128);
+#pragma unroll
+          for (int c = 0; c < 16; ++c) dst[c] = o[c];
+          if (kind >= 1 && re.k_cache != nullptr) {
+            const int slot = __ldg(re.slot_mapping + row);
+            if (slot >= 0) {
+              const int blk = slot / re.block_size, off = slot - blk * re.block_size;
+              const int kvh = kind == 1 ? head - re.H : head - re.H - re.Hkv;
+              uint4* cd = reinterpret_cast<uint4*>((kind == 1 ? re.k_cache : re.v_cache) + blk * re.blk_stride +
+                                                   off * re.tok_stride + kvh * re.head_stride);
+#pragma unroll
+              for (int c = 0; c < 16; ++c) cd[c] = o[c];
+            }
+          }
+        }
+      } else if constexpr (SILU) {
 #pragma unroll 1
         for (int c = 0; c < BN / 64; ++c) {
           uint32_t g[32], u[32];
@@ -241,11 +321,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   }
 }
 
-template <int BN, typename OutT, bool SILU = false, int CN = 1>
+template <int BN, typename OutT, bool SILU = false, int CN = 1, bool ROPE = false>
 static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy,
-                       cudaStream_t st) {
+                       cudaStream_t st, const RopeEpi& re = RopeEpi{}) {
   using C = GemmCfg<BN>;
-  auto kern = gemm_tcgen05_kernel<BN, OutT, SILU, CN>;
+  auto kern = gemm_tcgen05_kernel<BN, OutT, SILU, CN, ROPE>;
   static bool attr_set = false;
   if (!attr_set) {
     NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -258,7 +338,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
   const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
   if constexpr (CN == 1) {
     NVLLM_CUDA(launch_pdl(kern, dim3(clusters), dim3(256), C::kSmemBytes, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
-                          num_m_tiles, num_tiles));
+                          num_m_tiles, num_tiles, re));
   } else {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(clusters * CN);
@@ -272,7 +352,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles));
+    NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles, re));
   }
   return 0;
 }
@@ -412,4 +492,39 @@ extern "C" int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_
   NVLLM_CHECK_ARG(ldout == inter, NVLLM_ERR_ARG, "gemm_silu_mul: unfused path needs a contiguous output");
   if (int rc = nvllm_gemm_bf16(workspace, x, w_gate_up, m, 2 * inter, k, ldx, ldw, 2 * inter, NVLLM_BF16, nullptr, 0, stream)) return rc;
   return nvllm_silu_mul(out, workspace, m, inter, NVLLM_BF16, stream);
+}
+
+// QKVParallelLinear::forward (linear.rs:354-356) + q/k norm + RotaryEmbedding::forward + Attention::store_kv_cache
+// (qwen3.rs:219-229, attention.rs:150-174) in one kernel: qkv = x . Wqkv^T with the RopeEpi epilogue above.
+extern "C" int nvllm_gemm_qkv_rope_store(void* qkv, const void* x, const void* w_qkv, int32_t m, int32_t k, int64_t ldx,
+                                         int64_t ldw, const int64_t* positions, const float* cos_sin, const void* q_norm_w,
+                                         const void* k_norm_w, float eps, int32_t num_heads, int32_t num_kv_heads,
+                                         int32_t head_dim, int32_t max_position, void* k_cache, void* v_cache,
+                                         const int32_t* slot_mapping, const nvllm_kv_layout* layout, void* stream) {
+  using namespace nvllm;
+  NVLLM_CHECK_ARG(head_dim == 128, NVLLM_ERR_ARG, "gemm_qkv_rope_store: head_dim %d (128 only)", head_dim);
+  NVLLM_CHECK_ARG(m >= 0 && k > 0 && k % 64 == 0 && num_heads > 0 && num_kv_heads > 0 && max_position > 0, NVLLM_ERR_ARG,
+                  "gemm_qkv_rope_store: sizes");
+  if (m == 0) return 0;
+  NVLLM_CHECK_ARG(qkv && x && w_qkv && positions && cos_sin && aligned16(qkv) && aligned16(x) && aligned16(w_qkv),
+                  NVLLM_ERR_ALIGN, "gemm_qkv_rope_store: pointers");
+  NVLLM_CHECK_ARG((q_norm_w == nullptr) == (k_norm_w == nullptr), NVLLM_ERR_ARG, "gemm_qkv_rope_store: q/k norm weights");
+  RopeEpi re{};
+  re.positions = positions; re.cos_sin = cos_sin;
+  re.q_norm_w = static_cast<const bf16*>(q_norm_w); re.k_norm_w = static_cast<const bf16*>(k_norm_w);
+  re.H = num_heads; re.Hkv = num_kv_heads; re.max_position = max_position; re.eps = eps; re.block_size = 1;
+  if (k_cache != nullptr) {
+    NVLLM_CHECK_ARG(layout && v_cache && slot_mapping && layout->head_dim == 128 && layout->num_kv_heads == num_kv_heads &&
+                        layout->block_size > 0 && layout->token_stride % 8 == 0 && layout->head_stride % 8 == 0 &&
+                        layout->block_stride % 8 == 0,
+                    NVLLM_ERR_ARG, "gemm_qkv_rope_store: cache layout");
+    re.k_cache = static_cast<bf16*>(k_cache); re.v_cache = static_cast<bf16*>(v_cache); re.slot_mapping = slot_mapping;
+    re.block_size = layout->block_size; re.blk_stride = layout->block_stride; re.tok_stride = layout->token_stride;
+    re.head_stride = layout->head_stride;
+  }
+  const int n = (num_heads + 2 * num_kv_heads) * 128;
+  CUtensorMap tx, tw;
+  if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
+  if (int rc = make_tmap_bf16_2d(&tw, w_qkv, n, k, ldw, 128)) return rc;
+  return launch_gemm<128, bf16, false, 1, true>(tx, tw, qkv, m, n, k, n, static_cast<cudaStream_t>(stream), re);
 }

@@ -106,6 +106,7 @@ struct nvllm_runner {
   int last_decode_b = 0, last_decode_splits = 1;
   std::vector<int32_t> last_ctx;
   bool weights_ready = false;
+  bool fuse_rope = false; // NVLLM_FUSE_ROPE=1: qkv GEMM epilogue does q/k norm + RoPE + KV store for decode-sized batches
   bool fused_tp = false;  // h / normed / proj live in NVLink-mapped symmetric memory; all-reduce fused with add + RMSNorm
 
   ~nvllm_runner() {
@@ -176,6 +177,7 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   if (c.kv_layout == 1) { layout.token_stride = static_cast<int64_t>(Hkv) * D; layout.head_stride = D; }   // reference
   else { layout.token_stride = D; layout.head_stride = static_cast<int64_t>(bs) * D; }                     // head-major
 
+  { const char* e = getenv("NVLLM_FUSE_ROPE"); fuse_rope = e && e[0] == '1'; }
   NVLLM_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   // weights
   RUN(dalloc(&embed, static_cast<size_t>(vocab) * hidden));
@@ -430,10 +432,18 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
     // (and, under TP, with the all-reduce of that output: see add_norm below)
     if (l == 0) { RUN(nvllm_add_rmsnorm(normed, h, nullptr, w.input_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches; }
     else RUN(add_norm(w.input_ln));
-    RUN(gemm(qkv, normed, w.qkv, qkv_dim, hidden, qkv_dim, NVLLM_BF16));
-    // q/k norm + RoPE in place, K/V of this step into the cache (store before attention: note N2)
-    RUN(nvllm_qknorm_rope_store(qkv, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr, cfg.qk_norm ? w.k_norm : nullptr, eps,
-                                N, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l], d_slots, &layout, NVLLM_BF16, st)); ++launches;
+    if (fuse_rope && D == 128 && N <= 256) {
+      // decode-sized batches: qkv GEMM with q/k norm + RoPE + KV-cache store in its epilogue (one head per 128-wide tile)
+      ++launches;
+      RUN(nvllm_gemm_qkv_rope_store(qkv, normed, w.qkv, N, hidden, hidden, hidden, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr,
+                                    cfg.qk_norm ? w.k_norm : nullptr, eps, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l],
+                                    d_slots, &layout, st));
+    } else {
+      RUN(gemm(qkv, normed, w.qkv, qkv_dim, hidden, qkv_dim, NVLLM_BF16));
+      // q/k norm + RoPE in place, K/V of this step into the cache (store before attention: note N2)
+      RUN(nvllm_qknorm_rope_store(qkv, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr, cfg.qk_norm ? w.k_norm : nullptr, eps,
+                                  N, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l], d_slots, &layout, NVLLM_BF16, st)); ++launches;
+    }
     if (!is_prefill) {
       RUN(nvllm_paged_decode_attention(attn, qkv, kc[l], vc[l], d_tables, d_ctx, N, H, table_cap, qkv_dim, HD, &layout,
                                        scale, decode_ws, decode_ws_bytes, splits, NVLLM_BF16, st));

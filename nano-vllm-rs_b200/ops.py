@@ -115,6 +115,20 @@ def gemm_silu_mul(x, w_gate_up, out=None):
     return out
 
 
+def gemm_qkv_rope_store(x, w_qkv, positions, cos_sin, q_norm_w, k_norm_w, eps, num_heads, num_kv_heads, head_dim,
+                        k_cache=None, v_cache=None, slot_mapping=None, layout: KvLayout = None, out=None):
+    """qkv_proj + q/k norm + RoPE + store_kv_cache in one kernel (linear.rs:354-356, qwen3.rs:219-229, attention.rs:150-174)."""
+    _need(x, torch.bfloat16, "x"); _need(w_qkv, torch.bfloat16, "w_qkv"); _need(positions, torch.int64, "positions")
+    M, K = x.shape
+    n = (num_heads + 2 * num_kv_heads) * head_dim
+    if out is None:
+        out = torch.empty((M, n), dtype=torch.bfloat16, device=x.device)
+    check(_ffi.lib().nvllm_gemm_qkv_rope_store(_p(out), _p(x), _p(w_qkv), M, K, x.stride(0), w_qkv.stride(0), _p(positions),
+                                               _p(cos_sin), _p(q_norm_w), _p(k_norm_w), eps, num_heads, num_kv_heads, head_dim,
+                                               cos_sin.shape[0], _p(k_cache), _p(v_cache), _p(slot_mapping), layout, _stream()))
+    return out
+
+
 def add_rmsnorm(x, weight, eps, residual=None, out=None):
     """RMSNorm::forward (layernorm.rs:50-97). With `residual`, it is updated in place to bf16(residual + x)."""
     _need(x, torch.bfloat16, "x")

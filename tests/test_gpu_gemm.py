@@ -98,3 +98,35 @@ def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k):
     if m * inter * k < 2 ** 28:   # and against the CPU oracle where it is cheap
         want = O.silu_and_mul(O.linear(to_np_f32(x), to_np_f32(w)))
         assert_close(to_np_f32(fused), want, ATOL, 2 ** -6, "gemm_silu_mul vs oracle")
+
+
+@pytest.mark.parametrize("kind", ["reference", "head_major"])
+@pytest.mark.parametrize("m,H,Hkv,k,qknorm", [(256, 16, 8, 1024, True), (37, 4, 1, 512, True), (130, 8, 2, 256, False)])
+def test_gemm_qkv_rope_store_fused_equals_unfused(cuda, kind, m, H, Hkv, k, qknorm):
+    """qkv GEMM with the q/k-norm + RoPE + KV-store epilogue == nvllm_gemm_bf16 followed by nvllm_qknorm_rope_store
+    (bit-identical: same rounding points), for both cache layouts."""
+    from nano_vllm_rs_b200 import ops
+    from nano_vllm_rs_b200._ffi import KvLayout
+    D, bs = 128, 16
+    g = torch.Generator(device="cuda").manual_seed(m + H + k)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn(((H + 2 * Hkv) * D, k), generator=g, device=cuda) * 0.05).to(torch.bfloat16)
+    qw = (1 + 0.1 * torch.randn(D, generator=g, device=cuda)).to(torch.bfloat16) if qknorm else None
+    kw = (1 + 0.1 * torch.randn(D, generator=g, device=cuda)).to(torch.bfloat16) if qknorm else None
+    pos = torch.randint(0, 2048, (m,), generator=torch.Generator().manual_seed(1), dtype=torch.int64).to(cuda)
+    nblk = (m + bs - 1) // bs + 2
+    slots = torch.randperm(nblk * bs, generator=torch.Generator().manual_seed(2))[:m].to(torch.int32)
+    if m > 4:
+        slots[2] = -1
+    slots = slots.to(cuda)
+    table = ops.rope_table(2048, D, 1e6)
+    lay = KvLayout.reference(bs, Hkv, D) if kind == "reference" else KvLayout.head_major(bs, Hkv, D)
+    shape = (nblk, bs, Hkv, D) if kind == "reference" else (nblk, Hkv, bs, D)
+    kc1, vc1 = torch.zeros(shape, dtype=torch.bfloat16, device=cuda), torch.zeros(shape, dtype=torch.bfloat16, device=cuda)
+    kc2, vc2 = torch.zeros_like(kc1), torch.zeros_like(vc1)
+    fused = ops.gemm_qkv_rope_store(x, w, pos, table, qw, kw, 1e-6, H, Hkv, D, kc1, vc1, slots, lay)
+    ref = ops.gemm_bf16(x, w)
+    ops.qknorm_rope_store(ref, pos, table, qw, kw, 1e-6, H, Hkv, D, kc2, vc2, slots, lay)
+    torch.cuda.synchronize()
+    assert torch.equal(fused, ref)
+    assert torch.equal(kc1, kc2) and torch.equal(vc1, vc2)
