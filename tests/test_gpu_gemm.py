@@ -103,8 +103,8 @@ def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k):
 @pytest.mark.parametrize("kind", ["reference", "head_major"])
 @pytest.mark.parametrize("m,H,Hkv,k,qknorm", [(256, 16, 8, 1024, True), (37, 4, 1, 512, True), (130, 8, 2, 256, False)])
 def test_gemm_qkv_rope_store_fused_equals_unfused(cuda, kind, m, H, Hkv, k, qknorm):
-    """qkv GEMM with the q/k-norm + RoPE + KV-store epilogue == nvllm_gemm_bf16 followed by nvllm_qknorm_rope_store
-    (bit-identical: same rounding points), for both cache layouts."""
+    """qkv GEMM with the q/k-norm + RoPE + KV-store epilogue vs nvllm_gemm_bf16 followed by nvllm_qknorm_rope_store
+    (same rounding points), for both cache layouts."""
     from nano_vllm_rs_b200 import ops
     from nano_vllm_rs_b200._ffi import KvLayout
     D, bs = 128, 16
@@ -128,5 +128,13 @@ def test_gemm_qkv_rope_store_fused_equals_unfused(cuda, kind, m, H, Hkv, k, qkno
     ref = ops.gemm_bf16(x, w)
     ops.qknorm_rope_store(ref, pos, table, qw, kw, 1e-6, H, Hkv, D, kc2, vc2, slots, lay)
     torch.cuda.synchronize()
-    assert torch.equal(fused, ref)
-    assert torch.equal(kc1, kc2) and torch.equal(vc1, vc2)
+    # same rounding points; only the order of the 128-term sum of squares differs (thread-sequential vs warp shuffle), which
+    # can move a normalised value by one bf16 ulp before the rotation
+    assert_close(to_np_f32(fused), to_np_f32(ref), 2e-3, 2 ** -6, "fused qkv epilogue vs gemm + qknorm_rope_store")
+    assert torch.equal(fused[:, (H + Hkv) * D:], ref[:, (H + Hkv) * D:])            # v heads: pure GEMM output
+    assert (fused != ref).float().mean().item() < 0.02
+    # the cache holds exactly the k / v heads the kernel wrote to the qkv buffer (bit-exact data movement, slot -1 skipped)
+    kc3, vc3 = torch.zeros_like(kc1), torch.zeros_like(vc1)
+    ops.store_kvcache(fused[:, H * D:(H + Hkv) * D].view(m, Hkv, D), fused[:, (H + Hkv) * D:].view(m, Hkv, D), kc3, vc3, slots, lay)
+    torch.cuda.synchronize()
+    assert torch.equal(kc1, kc3) and torch.equal(vc1, vc3)
