@@ -204,6 +204,22 @@ int nvllm_argmax(int64_t* out_ids, float* out_max, const void* logits, int32_t b
 int nvllm_argmax_combine(int64_t* out_ids, const float* all_max, const int64_t* all_ids,
                          int32_t tp, int32_t batch, void* stream);
 
+/* K12 — replaces Sampler::forward / batch_sample / sample_single (src/layers/sampler.rs:26-106,221-254) with its
+ * helpers apply_top_k (:115-149), apply_top_p (:152-191), multinomial_sample (:194-203) and sample_gumbel (:205-219)
+ * for a whole batch in one launch (one CTA per row; selections instead of the reference's two full sorts).
+ * logits: f32 [batch, vocab] (leading dimension ld).  Per row b (all arrays are DEVICE pointers):
+ *   temperatures[b] == 0  -> greedy argmax, first maximum wins (sampler.rs:79-81)
+ *   otherwise s = logits / temperature; top_k[b] in (0, vocab) keeps the first k entries of the stable descending
+ *   order (0 or NULL array = None); top_p[b] in (0, 1) keeps the shortest descending prefix whose softmax mass
+ *   reaches p (other values or NULL array = None); token = argmax(s + gumbel), gumbel = -log(-log(u)).
+ * The reference draws u from an unseeded RNG; here u[j] = ((mix64(row_seeds[b] + (j+1)*0x9E3779B97F4A7C15) >> 41)
+ * + 0.5) * 2^-23 with mix64 = the splitmix64 finaliser — the same contract as oracle/layers.py, so a (seed, logits)
+ * pair always yields the same token.  kept_count (i32 [batch]) / kept_mask (u8 [batch, vocab]) are optional
+ * outputs describing the surviving set (parity tests); pass NULL in production. */
+int nvllm_sample(int64_t* out_ids, const float* logits, int32_t batch, int32_t vocab, int64_t ld,
+                 const float* temperatures, const int32_t* top_k, const float* top_p, const uint64_t* row_seeds,
+                 int32_t* kept_count, uint8_t* kept_mask, void* stream);
+
 /* C1 — the all-reduce the reference leaves as a TODO after o_proj / down_proj
  * (src/layers/linear.rs:236).  One communicator per process (one process per GPU).
  * nvllm_comm_unique_id writes NVLLM_UNIQUE_ID_BYTES bytes on rank 0; the caller broadcasts them

@@ -358,11 +358,8 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
 }
 
 static int pick_bn(int M, int N) {
-  static int forced = -1;
-  if (forced < 0) {
-    const char* e = getenv("NVLLM_GEMM_BN");  // benchmarking knob
-    forced = e ? atoi(e) : 0;
-  }
+  const char* e = getenv("NVLLM_GEMM_BN");  // benchmarking knob, re-read per call so one process can sweep it
+  const int forced = e ? atoi(e) : 0;
   if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
   const int sms = sm_count();
   const long mt = (M + 127) / 128;
@@ -397,21 +394,13 @@ static bool want_2cta(int m, int n, int k) {
 }
 
 static bool use_mcast() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("NVLLM_GEMM_MCAST");  // A/B knob: 0 disables the x-multicast clusters
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v == 1;
+  const char* e = getenv("NVLLM_GEMM_MCAST");  // A/B knob: 0 disables the x-multicast clusters
+  return !(e && e[0] == '0');
 }
 
 static bool use_2cta() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("NVLLM_GEMM_2CTA");  // A/B knob: 0 keeps every shape on the single-CTA kernel
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v == 1;
+  const char* e = getenv("NVLLM_GEMM_2CTA");  // A/B knob: 0 keeps every shape on the single-CTA kernel
+  return !(e && e[0] == '0');
 }
 
 }  // namespace nvllm

@@ -247,11 +247,8 @@ static int pick_bn_2cta(int M, int N) {
 
 int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw,
                        int64_t ldy, int out_dtype, cudaStream_t st) {
-  static int forced = -1;
-  if (forced < 0) {
-    const char* e = getenv("NVLLM_GEMM_BN");
-    forced = e ? atoi(e) : 0;
-  }
+  const char* e = getenv("NVLLM_GEMM_BN");
+  const int forced = e ? atoi(e) : 0;
   const int bn = (forced == 64 || forced == 128 || forced == 256) ? forced : pick_bn_2cta(m, n);
   CUtensorMap tx, tw;
   if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;

@@ -204,6 +204,25 @@ def argmax_combine(all_max, all_ids):
     return out
 
 
+def sample(logits, temperatures, row_seeds, top_k=None, top_p=None, debug=False):
+    """Sampler::forward (sampler.rs:26-106): temperature / top-k / top-p / Gumbel-max per row, greedy where T == 0.
+    logits f32 [B, V]; temperatures f32 [B]; row_seeds: uint64 values (any int64/uint64 tensor of bit patterns) [B];
+    top_k i32 [B] / top_p f32 [B] optional.  debug=True also returns (kept_count i32 [B], kept_mask u8 [B, V])."""
+    _need(logits, torch.float32, "logits"); _need(temperatures, torch.float32, "temperatures")
+    assert logits.stride(1) == 1 and row_seeds.element_size() == 8 and row_seeds.is_cuda
+    if top_k is not None:
+        _need(top_k, torch.int32, "top_k")
+    if top_p is not None:
+        _need(top_p, torch.float32, "top_p")
+    B, V = logits.shape
+    ids = torch.empty(B, dtype=torch.int64, device=logits.device)
+    cnt = torch.empty(B, dtype=torch.int32, device=logits.device) if debug else None
+    mask = torch.empty((B, V), dtype=torch.uint8, device=logits.device) if debug else None
+    check(_ffi.lib().nvllm_sample(_p(ids), _p(logits), B, V, logits.stride(0), _p(temperatures), _p(top_k), _p(top_p),
+                                  _p(row_seeds), _p(cnt), _p(mask), _stream()))
+    return (ids, cnt, mask) if debug else ids
+
+
 def init_weight(shape, seed, tensor_id, std, dtype=torch.bfloat16, device="cuda"):
     t = torch.empty(shape, dtype=dtype, device=device)
     check(_ffi.lib().nvllm_init_weight(_p(t), t.numel(), seed, tensor_id, std, BF16 if dtype == torch.bfloat16 else F32, _stream()))

@@ -215,3 +215,95 @@ def extract_last_tokens(x, cu_seqlens_q):
 def greedy_sample(logits):
     """Sampler::greedy_sample, sampler.rs:109-112: argmax over the vocab (first maximum)."""
     return np.argmax(logits, axis=-1).astype(np.int64)
+
+
+# ---------------------------------------------------------------------------- sampler (SURVEY.md §8f #3)
+#
+# Sampler::forward / sample_single / apply_top_k / apply_top_p / multinomial_sample / sample_gumbel, sampler.rs:26-219.
+# The reference draws its uniforms from an UNSEEDED Tensor::rand (sampler.rs:208), so its random draws cannot be
+# reproduced by anyone; the build fixes a seeded, counter-based contract instead (identical here and on the GPU):
+#   row_seed  = mix64(engine_seed ^ mix64(seq_id * GOLDEN + num_tokens_of_the_sequence))
+#   u[j]      = ((mix64(row_seed + (j + 1) * GOLDEN) >> 41) + 0.5) * 2^-23          in (0, 1), exact in f32
+#   gumbel[j] = -log(-log(clamp(u[j], 1e-8, 1 - 1e-8)))                              sampler.rs:211-216, f32
+# Other deliberate readings of the reference: top_k == 0 means "no top-k" (batch_sample maps None to 0, which the
+# reference would then index at k - 1 = usize::MAX, sampler.rs:243,131); top_p >= 1 or <= 0 means "no top-p".
+
+GOLDEN = np.uint64(0x9E3779B97F4A7C15)
+
+
+def mix64(x):
+    """splitmix64 finaliser on uint64 (arrays or scalars), wrap-around arithmetic."""
+    with np.errstate(over="ignore"):
+        x = np.asarray(x, dtype=np.uint64)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+
+
+def sampler_row_seed(engine_seed, seq_id, num_tokens):
+    with np.errstate(over="ignore"):
+        inner = mix64(np.uint64(seq_id) * GOLDEN + np.uint64(num_tokens))
+        return int(mix64(np.uint64(engine_seed) ^ inner))
+
+
+def sampler_uniform(row_seed, n):
+    with np.errstate(over="ignore"):
+        j = np.arange(1, n + 1, dtype=np.uint64)
+        h = mix64(np.uint64(row_seed) + j * GOLDEN)
+    return ((h >> np.uint64(41)).astype(np.float32) + np.float32(0.5)) * np.float32(2.0 ** -23)
+
+
+def sample_gumbel(u):
+    """sample_gumbel, sampler.rs:205-219 (f32)."""
+    eps = np.float32(1e-8)
+    uc = np.clip(u.astype(np.float32), eps, np.float32(1.0) - eps)
+    return -np.log(-np.log(uc))
+
+
+def apply_top_k(logits, k):
+    """apply_top_k, sampler.rs:115-149: the first k entries of the stable descending sort survive, the rest -> -inf."""
+    v = logits.shape[0]
+    k = min(int(k), v)
+    order = np.argsort(-logits, kind="stable")  # sort_by(b.partial_cmp(a)) is stable: ties keep index order
+    out = np.full(v, -np.inf, dtype=np.float32)
+    out[order[:k]] = logits[order[:k]]
+    return out
+
+
+def apply_top_p(logits, p):
+    """apply_top_p, sampler.rs:152-191: softmax, stable descending sort, sequential f32 cumulative sum, keep entries up to
+    and including the first one at which the running sum reaches p (all of them if it never does)."""
+    v = logits.shape[0]
+    m = np.max(logits)
+    e = np.exp(logits - m).astype(np.float32)
+    probs = e / np.sum(e, dtype=np.float32)
+    order = np.argsort(-probs, kind="stable")
+    cum = np.cumsum(probs[order], dtype=np.float32)  # numpy's cumsum is the sequential recurrence
+    hit = np.nonzero(cum >= np.float32(p))[0]
+    cutoff = int(hit[0]) + 1 if hit.size else v
+    out = np.full(v, -np.inf, dtype=np.float32)
+    out[order[:cutoff]] = logits[order[:cutoff]]
+    return out
+
+
+def sample_single(logits, temperature, top_p, top_k, row_seed):
+    """sample_single, sampler.rs:70-106.  Returns (token, filtered logits, scores = filtered + gumbel or None)."""
+    logits = np.asarray(logits, dtype=np.float32)
+    if temperature == 0.0:
+        return int(np.argmax(logits)), logits, None
+    s = logits / np.float32(temperature) if temperature != 1.0 else logits.copy()
+    if top_k:
+        s = apply_top_k(s, top_k)
+    if top_p is not None and 0.0 < top_p < 1.0:
+        s = apply_top_p(s, top_p)
+    scores = s + sample_gumbel(sampler_uniform(row_seed, logits.shape[0]))
+    return int(np.argmax(scores)), s, scores
+
+
+def sampler_forward(logits, temperatures, top_p, top_k, row_seeds):
+    """Sampler::forward / batch_sample, sampler.rs:26-67,221-254: one sample_single per row."""
+    out = np.zeros(len(temperatures), dtype=np.int64)
+    for i in range(len(temperatures)):
+        out[i], _, _ = sample_single(logits[i], float(temperatures[i]), None if top_p is None else float(top_p[i]),
+                                     None if top_k is None else int(top_k[i]), int(row_seeds[i]))
+    return out
