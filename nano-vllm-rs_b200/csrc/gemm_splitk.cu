@@ -1,0 +1,305 @@
+// gemm_splitk.cu — K5'': split-K variant of the tcgen05 GEMM for the decode-sized projections (M <= 256 rows).
+//
+// Why: measured in-graph (profiles/r01_gemm_ingraph_v1.jsonl) the small-M GEMMs cost ~0.31 us per 64-wide k-block per
+// CTA whatever the tile width — each SM can only ingest ~35-45 B/clk through TMA, and every CTA of a 128 x BN tile has
+// to pull (128 + BN) x K x 2 bytes on its own (the x tile is re-read by every n-tile; multicasting it does not help,
+// the bytes still have to enter each SM).  o_proj / down_proj of Qwen3-0.6B (N = 1024, K = 2048 / 3072) run on only
+// 64 CTAs at 12-17 us while their weights would stream from HBM in ~1 us.
+// What: a cluster of SK CTAs shares one 128 x BN output tile and splits K: per-CTA ingest drops to
+// (128 + BN) x K / SK x 2 bytes, all SMs pull in parallel and wide tiles (good x reuse) become affordable.  Each CTA
+// accumulates its partial tile in TMEM, parks it as f32 in its own shared memory (over the drained operand ring), and
+// after one cluster barrier every CTA reduces BN / SK columns of the tile over distributed shared memory in FIXED rank
+// order (deterministic, independent of timing) and writes its slice of y.  No workspace, no atomics, no second kernel.
+// Same contract as nvllm_gemm_bf16 / nvllm_gemm_silu_mul_bf16 with bf16 output (LinearBase::forward, linear.rs:228-239;
+// MergedColumnParallelLinear + SiluAndMul, linear.rs:437-439 + activation.rs:46-63).
+#include "tc.cuh"
+
+namespace nvllm {
+namespace {
+
+template <int BN>
+struct SkCfg {
+  static constexpr int BM = 128, BK = 64;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (192 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kRingBytes = kStages * kStageBytes;
+  static constexpr int kPartialBytes = BN * BM * 4;  // f32 partial tile, column-major [BN][128]
+  static_assert(kPartialBytes <= kRingBytes, "the partial tile is parked over the operand ring");
+  static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+  static constexpr int kBarBytes = (2 * kStages + 1) * 8 + 16;
+  static constexpr int kSmemBytes = kRingBytes + kBarBytes + 1024;
+};
+
+__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];\n" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_smem_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;\n" ::"r"(addr), "f"(v) : "memory");
+}
+
+// One cluster of SK CTAs per (m_tile, n_tile); cluster rank r accumulates k-blocks [r * kb_per, (r + 1) * kb_per).
+// SILU: w = [gate (N rows) | up (N rows)], the B tile is BN/2 gate rows + the matching BN/2 up rows, y[:, BN/2 per tile].
+template <int BN, int SK, bool SILU>
+__global__ void __launch_bounds__(256, 1)
+gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                   bf16* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles) {
+  using C = SkCfg<BN>;
+  constexpr int STAGES = C::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA = smem_base;
+  const uint32_t sB = smem_base + STAGES * C::kABytes;
+  const uint32_t bars = smem_base + C::kRingBytes;
+  auto full_bar = [&](int s) { return bars + s * 8; };
+  auto empty_bar = [&](int s) { return bars + (STAGES + s) * 8; };
+  const uint32_t tfull_bar = bars + 2 * STAGES * 8;
+  const uint32_t tmem_slot = bars + (2 * STAGES + 1) * 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = static_cast<int>(cluster_ctarank());
+  const int tile = static_cast<int>(blockIdx.x) / SK;
+  const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
+  const int kb_per = (K / C::BK) / SK, kb0 = rank * kb_per;
+  pdl_launch_dependents();
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<C::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer: weights first (independent of the predecessor kernel), x after the dependency wait =====
+    auto load_w = [&](int stage, int kb) {
+      if constexpr (SILU) {
+        tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * (BN / 2));
+        tma_load_2d(sB + stage * C::kBBytes + (BN / 2) * 128, &tmap_w, full_bar(stage), kb * C::BK, N + n_tile * (BN / 2));
+      } else {
+        tma_load_2d(sB + stage * C::kBBytes, &tmap_w, full_bar(stage), kb * C::BK, n_tile * BN);
+      }
+    };
+    const int pre = kb_per < STAGES ? kb_per : STAGES;
+    for (int i = 0; i < pre; ++i) {
+      mbar_expect_tx(full_bar(i), C::kStageBytes);
+      load_w(i, kb0 + i);
+    }
+    pdl_wait();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < kb_per; ++i) {
+      if (i >= pre) {
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        mbar_expect_tx(full_bar(stage), C::kStageBytes);
+        load_w(stage, kb0 + i);
+      }
+      tma_load_2d(sA + stage * C::kABytes, &tmap_x, full_bar(stage), (kb0 + i) * C::BK, m_tile * C::BM);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = umma_idesc_bf16(C::BM, BN, 0, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < kb_per; ++i) {
+      mbar_wait(full_bar(stage), phase);
+      tc_fence_after();
+      const uint32_t a0 = sA + stage * C::kABytes, b0 = sB + stage * C::kBBytes;
+#pragma unroll
+      for (int k = 0; k < C::BK / 16; ++k)
+        umma_bf16_ss(tmem_base, umma_desc_sw128(a0 + k * 32, 16, 1024), umma_desc_sw128(b0 + k * 32, 16, 1024), idesc,
+                     (i | k) != 0 ? 1u : 0u);
+      umma_commit(empty_bar(stage));
+      if (i == kb_per - 1) umma_commit(tfull_bar);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===== park the partial tile: TMEM -> f32 shared memory, column-major (lanes = rows: conflict-free) =====
+    const int q = warp & 3;
+    mbar_wait(tfull_bar, 0);  // every MMA has retired: the operand ring is dead and can be overwritten
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t prow = smem_base + (q * 32 + lane) * 4;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(taddr + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) st_smem_f32(prow + (c * 32 + e) * (C::BM * 4), __uint_as_float(r[e]));
+    }
+    tc_fence_before();
+  }
+  __syncwarp();
+  cluster_sync_all();  // all SK partial tiles are parked and visible cluster-wide
+
+  if (warp >= 4) {
+    // ===== reduce this CTA's column slice over the cluster in fixed rank order, then the usual epilogue =====
+    pdl_wait();  // y may still be read by an earlier kernel until the predecessor has completed
+    const int q = warp & 3;
+    const int row_in = q * 32 + lane;
+    const int row = m_tile * C::BM + row_in;
+    uint32_t peer[SK];
+#pragma unroll
+    for (int r = 0; r < SK; ++r) peer[r] = dsmem_addr(smem_base + row_in * 4, static_cast<uint32_t>(r));
+    if constexpr (SILU) {
+      constexpr int CW = BN / (2 * SK);  // output columns of this CTA
+      static_assert(CW >= 8 && CW % 8 == 0, "slice must be whole 16-byte vectors");
+      bf16* dst = y + row * ldy + n_tile * (BN / 2) + rank * CW;
+#pragma unroll 1
+      for (int j = 0; j < CW; j += 8) {
+        float g[8], u[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int cg = rank * CW + j + e, cu = BN / 2 + cg;
+          float sg = 0.f, su = 0.f;
+#pragma unroll
+          for (int r = 0; r < SK; ++r) {
+            sg += ld_dsmem_f32(peer[r] + cg * (C::BM * 4));
+            su += ld_dsmem_f32(peer[r] + cu * (C::BM * 4));
+          }
+          g[e] = sg; u[e] = su;
+        }
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) {  // rounding points of the unfused path: bf16 gate_up, bf16 silu(gate), bf16 product
+          const uint32_t gb = pack_bf16x2(g[e], g[e + 1]);
+          const uint32_t ub = pack_bf16x2(u[e], u[e + 1]);
+          const float g0 = bf16_lo(gb), g1 = bf16_hi(gb);
+          const uint32_t sb = pack_bf16x2(g0 / (1.0f + expf(-g0)), g1 / (1.0f + expf(-g1)));
+          o[e / 2] = pack_bf16x2(bf16_lo(sb) * bf16_lo(ub), bf16_hi(sb) * bf16_hi(ub));
+        }
+        if (row < M) *reinterpret_cast<uint4*>(dst + j) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    } else {
+      constexpr int CW = BN / SK;
+      static_assert(CW >= 8 && CW % 8 == 0, "slice must be whole 16-byte vectors");
+      bf16* dst = y + row * ldy + n_tile * BN + rank * CW;
+#pragma unroll 1
+      for (int j = 0; j < CW; j += 8) {
+        float a[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int c = rank * CW + j + e;
+          float s = 0.f;
+#pragma unroll
+          for (int r = 0; r < SK; ++r) s += ld_dsmem_f32(peer[r] + c * (C::BM * 4));
+          a[e] = s;
+        }
+        if (row < M)
+          *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16x2(a[0], a[1]), pack_bf16x2(a[2], a[3]),
+                                                          pack_bf16x2(a[4], a[5]), pack_bf16x2(a[6], a[7]));
+      }
+    }
+  }
+  __syncwarp();
+  cluster_sync_all();  // nobody leaves while a peer may still read its partial tile
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
+}
+
+template <int BN, int SK, bool SILU>
+int launch_splitk(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy, int tiles,
+                  int num_m_tiles, cudaStream_t st) {
+  using C = SkCfg<BN>;
+  auto kern = gemm_splitk_kernel<BN, SK, SILU>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(tiles * SK);
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = SK; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<bf16*>(y), M, N, K, ldy, num_m_tiles));
+  return 0;
+}
+
+// Bytes one CTA has to ingest (operands) plus park + reduce (partial tile written once, one tile's worth read back).
+long splitk_cost(int bn, int sk, int k) { return 2l * (128 + bn) * (k / sk) + (sk > 1 ? 2l * bn * 512 : 0); }
+
+}  // namespace
+
+// Chooses (BN, SK) for y[m, n] = x . w^T (accumulator width n_acc = n, or 2 * inter for the SiLU form); returns false
+// when no split-K configuration beats the single-CTA tile `bn_default` by a clear margin.  NVLLM_GEMM_SPLITK:
+// "0" = never, "BN,SK" = force that configuration where it is legal, unset / "1" = the cost model below.
+bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_bn, int* out_sk) {
+  const char* e = getenv("NVLLM_GEMM_SPLITK");
+  if (e && e[0] == '0' && e[1] == 0) return false;
+  if (m > 256 || k % 64 != 0) return false;
+  const int sms = sm_count();
+  const int mt = (m + 127) / 128, num_kb = k / 64;
+  auto legal = [&](int bn, int sk) {
+    if (n_acc % bn != 0 || num_kb % sk != 0 || num_kb / sk < 1) return false;
+    if ((silu ? bn / (2 * sk) : bn / sk) < 8 || (bn == 64 && sk == 8)) return false;
+    return static_cast<long>(mt) * (n_acc / bn) * sk <= sms;
+  };
+  int fbn = 0, fsk = 0;
+  if (e && sscanf(e, "%d,%d", &fbn, &fsk) == 2) {
+    const bool known = (fbn == 64 || fbn == 128 || fbn == 256) && (fsk == 2 || fsk == 4 || fsk == 8);
+    if (known && legal(fbn, fsk)) { *out_bn = fbn; *out_sk = fsk; return true; }
+    return false;
+  }
+  const int bns[3] = {256, 128, 64}, sks[3] = {8, 4, 2};
+  long best = -1;
+  for (int bn : bns)
+    for (int sk : sks) {
+      if (!legal(bn, sk)) continue;
+      const long c = splitk_cost(bn, sk, k);
+      if (best < 0 || c < best) { best = c; *out_bn = bn; *out_sk = sk; }
+    }
+  if (best < 0) return false;
+  const long tiles_d = static_cast<long>(mt) * ((n_acc + bn_default - 1) / bn_default);
+  const long waves_d = (tiles_d + sms - 1) / sms;
+  return best * 10 < splitk_cost(bn_default, 1, k) * waves_d * 7;  // at least 30 % fewer bytes per SM
+}
+
+int gemm_splitk_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw, int64_t ldy,
+                         bool silu, int bn, int sk, cudaStream_t st) {
+  CUtensorMap tx, tw;
+  const int n_acc = silu ? 2 * n : n;
+  if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
+  if (int rc = make_tmap_bf16_2d(&tw, w, n_acc, k, ldw, silu ? bn / 2 : bn)) return rc;
+  const int mt = (m + 127) / 128, tiles = mt * (n_acc / bn);
+#define NVLLM_SK(BNV, SKV)                                                                                   \
+  if (bn == BNV && sk == SKV)                                                                                \
+    return silu ? launch_splitk<BNV, SKV, true>(tx, tw, y, m, n, k, ldy, tiles, mt, st)                      \
+                : launch_splitk<BNV, SKV, false>(tx, tw, y, m, n, k, ldy, tiles, mt, st)
+  NVLLM_SK(256, 8); NVLLM_SK(256, 4); NVLLM_SK(256, 2);
+  NVLLM_SK(128, 8); NVLLM_SK(128, 4); NVLLM_SK(128, 2);
+  NVLLM_SK(64, 4); NVLLM_SK(64, 2);
+#undef NVLLM_SK
+  NVLLM_CHECK_ARG(false, NVLLM_ERR_ARG, "gemm_splitk: no kernel for bn=%d sk=%d", bn, sk);
+}
+
+}  // namespace nvllm

@@ -380,6 +380,11 @@ int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int 
 int gemm_silu_2cta_dispatch(void* y, const void* x, const void* w, int m, int inter, int k, int64_t ldx, int64_t ldw,
                             int64_t ldy, cudaStream_t st);  // gemm_tcgen05_2cta.cu
 
+// gemm_splitk.cu: cluster split-K for decode-sized projections (m <= 256)
+bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_bn, int* out_sk);
+int gemm_splitk_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw, int64_t ldy,
+                         bool silu, int bn, int sk, cudaStream_t st);
+
 static bool use_2cta();
 // CTA pairs pay off once there are at least two 256-row tiles or the problem is large enough to fill the machine with
 // 256 x 256 tiles; between 129 and 511 rows the single-CTA kernel (more, narrower, single-wave tiles) measured faster
@@ -419,10 +424,14 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   NVLLM_CHECK_ARG(out_dtype == NVLLM_BF16 || out_dtype == NVLLM_F32, NVLLM_ERR_DTYPE, "gemm: out_dtype %d", out_dtype);
   if (m == 0) return 0;
   NVLLM_CHECK_ARG(y && x && w && aligned16(y) && aligned16(x) && aligned16(w), NVLLM_ERR_ALIGN, "gemm: pointers");
-  if (want_2cta(m, n, k))
-    return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, static_cast<cudaStream_t>(stream));
-  const int bn = pick_bn(m, n);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (out_dtype == NVLLM_BF16) {  // decode-sized, long-K projections: split K over a cluster (gemm_splitk.cu)
+    int sbn = 0, ssk = 0;
+    if (splitk_choose(m, n, k, false, pick_bn(m, n), &sbn, &ssk))
+      return gemm_splitk_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, false, sbn, ssk, st);
+  }
+  if (want_2cta(m, n, k)) return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, st);
+  const int bn = pick_bn(m, n);
   CUtensorMap tx, tw;
   // x-multicast clusters of 4 along N: worth it when x (re-read once per n-tile) dominates the L2 -> SM traffic,
   // i.e. several n-tiles of a narrow width and a long K.
@@ -463,8 +472,13 @@ extern "C" int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_
   (void)workspace; (void)workspace_bytes;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (inter % 128 == 0) {  // fused epilogue: the [m, 2*inter] tensor never exists
-    if (want_2cta(m, 2 * inter, k)) return gemm_silu_2cta_dispatch(out, x, w_gate_up, m, inter, k, ldx, ldw, ldout, st);
     const int bn = pick_bn(m, 2 * inter) < 64 ? 64 : pick_bn(m, 2 * inter);
+    {
+      int sbn = 0, ssk = 0;
+      if (splitk_choose(m, 2 * inter, k, true, bn, &sbn, &ssk))
+        return gemm_splitk_dispatch(out, x, w_gate_up, m, inter, k, ldx, ldw, ldout, true, sbn, ssk, st);
+    }
+    if (want_2cta(m, 2 * inter, k)) return gemm_silu_2cta_dispatch(out, x, w_gate_up, m, inter, k, ldx, ldw, ldout, st);
     CUtensorMap tx, tw;
     if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
     if (int rc = make_tmap_bf16_2d(&tw, w_gate_up, 2 * static_cast<int64_t>(inter), k, ldw, bn / 2)) return rc;

@@ -138,3 +138,60 @@ def test_gemm_qkv_rope_store_fused_equals_unfused(cuda, kind, m, H, Hkv, k, qkno
     ops.store_kvcache(fused[:, H * D:(H + Hkv) * D].view(m, Hkv, D), fused[:, (H + Hkv) * D:].view(m, Hkv, D), kc3, vc3, slots, lay)
     torch.cuda.synchronize()
     assert torch.equal(kc1, kc3) and torch.equal(vc1, vc3)
+
+
+SPLITK_CFGS = ["64,2", "64,4", "128,2", "128,4", "128,8", "256,2", "256,4", "256,8"]
+
+
+@pytest.mark.parametrize("cfg", SPLITK_CFGS)
+def test_gemm_splitk_every_config_vs_device_check(cuda, cfg, monkeypatch):
+    """Cluster split-K GEMM (gemm_splitk.cu), every (BN, SK) instantiation forced through NVLLM_GEMM_SPLITK (re-read per
+    call): M tail rows, K split 2/4/8 ways, against the CUDA-core check kernel and the same GEMM without split-K."""
+    from nano_vllm_rs_b200 import ops
+    m, n, k = 200, 1024, 2048
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn((n, k), generator=g, device=cuda) * 0.05).to(torch.bfloat16)
+    r = ops.gemm_bf16(x, w, out_dtype=torch.float32, simt=True)
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", "0")
+    base = ops.gemm_bf16(x, w)
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", cfg)
+    y = ops.gemm_bf16(x, w)
+    y2 = ops.gemm_bf16(x, w)
+    torch.cuda.synchronize()
+    assert_close(to_np_f32(y), to_np_f32(r), ATOL, RTOL, f"split-K {cfg} vs check kernel")
+    assert torch.equal(y, y2), "fixed-order cluster reduction must be deterministic"
+    # the un-split kernel sums the same products in another order: at most one bf16 ulp apart, mostly identical
+    assert_close(to_np_f32(y), to_np_f32(base), 1e-3, 2 ** -7, f"split-K {cfg} vs un-split")
+    assert (y != base).float().mean().item() < 0.05
+
+
+@pytest.mark.parametrize("cfg", SPLITK_CFGS)
+def test_gemm_splitk_silu_every_config_vs_oracle(cuda, cfg, monkeypatch):
+    from nano_vllm_rs_b200 import ops
+    m, inter, k = 200, 512, 1024
+    rng = np.random.default_rng(5)
+    x = randn_bf16(rng, (m, k)); w = randn_bf16(rng, (2 * inter, k), 0.05)
+    xd, wd = to_dev_bf16(x, cuda), to_dev_bf16(w, cuda)
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", cfg)
+    y = ops.gemm_silu_mul(xd, wd)
+    torch.cuda.synchronize()
+    want = O.silu_and_mul(O.linear(x, w))
+    assert_close(to_np_f32(y), want, ATOL, 2 ** -6, f"split-K silu {cfg} vs oracle")
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", "0")
+    base = ops.gemm_silu_mul(xd, wd)
+    torch.cuda.synchronize()
+    assert (y != base).float().mean().item() < 0.05
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 1024, 3072), (256, 1024, 2048), (4, 1024, 3072), (64, 2048, 4096), (1, 1024, 2048)])
+def test_gemm_splitk_auto_decode_shapes(cuda, m, n, k):
+    """The shapes the cost model sends to split-K by default (Qwen3-0.6B o_proj / down_proj at decode) vs the check kernel."""
+    from nano_vllm_rs_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(m + n + k)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn((n, k), generator=g, device=cuda) * 0.02).to(torch.bfloat16)
+    y = ops.gemm_bf16(x, w)
+    r = ops.gemm_bf16(x, w, out_dtype=torch.float32, simt=True)
+    torch.cuda.synchronize()
+    assert_close(to_np_f32(y), to_np_f32(r), ATOL, RTOL, f"auto split-K {m}x{n}x{k}")

@@ -10,13 +10,19 @@ from nano_vllm_rs_b200 import ops  # noqa: E402
 SHAPES = {  # name: (M, N, K, kind)
     "0.6B qkv": (256, 4096, 1024, "gemm"), "0.6B o": (256, 1024, 2048, "gemm"), "0.6B gate_up+silu": (256, 3072, 1024, "silu"),
     "0.6B down": (256, 1024, 3072, "gemm"),
+    "8B m256 qkv": (256, 6144, 4096, "gemm"), "8B m256 o": (256, 4096, 4096, "gemm"), "8B m256 gate_up+silu": (256, 12288, 4096, "silu"),
+    "8B m256 down": (256, 4096, 12288, "gemm"),
+    "32B/tp8 m64 qkv": (64, 1280, 5120, "gemm"), "32B/tp8 m64 o": (64, 5120, 1024, "gemm"),
+    "32B/tp8 m64 gate_up+silu": (64, 3200, 5120, "silu"), "32B/tp8 m64 down": (64, 5120, 3200, "gemm"),
     "8B/tp2 qkv": (512, 3072, 4096, "gemm"), "8B/tp2 o": (512, 4096, 2048, "gemm"), "8B/tp2 gate_up+silu": (512, 6144, 4096, "silu"),
     "8B/tp2 down": (512, 4096, 6144, "gemm"),
     "8B/tp8 qkv": (512, 768, 4096, "gemm"), "8B/tp8 o": (512, 4096, 512, "gemm"), "8B/tp8 gate_up+silu": (512, 1536, 4096, "silu"),
     "8B/tp8 down": (512, 4096, 1536, "gemm"),
 }
-KNOBS = [{}, {"NVLLM_GEMM_BN": "32"}, {"NVLLM_GEMM_BN": "64"}, {"NVLLM_GEMM_BN": "128"}, {"NVLLM_GEMM_MCAST": "0"},
-         {"NVLLM_GEMM_2CTA": "0"}]
+KNOBS = [{}, {"NVLLM_GEMM_SPLITK": "0"}, {"NVLLM_GEMM_SPLITK": "64,4"}, {"NVLLM_GEMM_SPLITK": "128,2"},
+         {"NVLLM_GEMM_SPLITK": "128,4"}, {"NVLLM_GEMM_SPLITK": "128,8"}, {"NVLLM_GEMM_SPLITK": "256,2"},
+         {"NVLLM_GEMM_SPLITK": "256,4"}, {"NVLLM_GEMM_SPLITK": "256,8"}, {"NVLLM_GEMM_SPLITK": "0", "NVLLM_GEMM_MCAST": "0"},
+         {"NVLLM_GEMM_SPLITK": "0", "NVLLM_GEMM_2CTA": "0"}]
 ALL = ("NVLLM_GEMM_BN", "NVLLM_GEMM_MCAST", "NVLLM_GEMM_2CTA", "NVLLM_GEMM_SPLITK")
 
 
