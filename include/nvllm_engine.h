@@ -36,7 +36,7 @@ typedef struct nvllm_config {
   int32_t num_attention_heads, num_key_value_heads, head_dim, max_position_embeddings;
   int32_t tie_word_embeddings, qk_norm;
   int32_t kv_layout;              /* 0 = head-major [blk,Hkv,bs,D] (engine default), 1 = reference [blk,bs,Hkv,D] */
-  int32_t reserved;
+  int32_t sampling_seed;          /* engine seed of the sampler's counter-based uniforms (nvllm.h, nvllm_sample) */
   float rms_norm_eps;
   float reserved_f;
   double rope_theta;
@@ -49,8 +49,10 @@ int nvllm_config_init(nvllm_config* cfg, const char* arch);
 /* Config::validate (config.rs:83-119) + Qwen3Config::validate (qwen3.rs:106-123) on the fields above. */
 int nvllm_config_validate(const nvllm_config* cfg);
 
-/* SamplingParams (sampling_params.rs:10-88). Only temperature == 0 (greedy, sampler.rs:79-81) is executed on the
- * device in this round; other values are accepted as data and rejected at execution time. */
+/* SamplingParams (sampling_params.rs:10-88).  temperature == 0 is greedy (sampler.rs:79-81); otherwise temperature /
+ * top-k / top-p / Gumbel-max sampling runs on the device (nvllm_sample) with tensor_parallel_size == 1 — under TP the
+ * logits are vocab-sharded and only greedy decoding is wired (rejected loudly otherwise).  repetition_penalty is carried
+ * but unused, as in the reference (sampler.rs:26-67 never reads it). */
 typedef struct nvllm_sampling_params {
   float temperature; /* reference default 1.0 */
   int32_t max_tokens; /* 64 */
@@ -78,6 +80,8 @@ typedef struct nvllm_batch {
   const int32_t* context_lens; /* [num_seqs]   (decode)  */
   const int32_t* block_tables; /* [num_seqs, max_blocks] padded with -1 (decode; prefill iff has_block_tables) */
   const float* temperatures;   /* [num_seqs] */
+  const int32_t* top_k;        /* [num_seqs], 0 = None */
+  const float* top_p;          /* [num_seqs], 0 = None */
 } nvllm_batch;
 
 /* Scheduler (scheduler.rs:14-334) owning a BlockManager (block_manager.rs:69-331) and the Sequences
@@ -119,7 +123,8 @@ int nvllm_runner_init_weights(nvllm_runner* r, uint64_t seed, float std);
  * q/k/v -> qkv_proj, gate/up -> gate_up_proj (utils/loader.rs:175-198; linear.rs:154-172,249-267). */
 int nvllm_runner_load_weight(nvllm_runner* r, const char* name, const void* h_bf16, int64_t rows, int64_t cols);
 /* ModelRunner::execute_model + sample_tokens (model_runner.rs:105-156): runs the forward for `batch`, writes the
- * greedy token of every sequence to h_tokens[num_seqs].  h_logits (nullable): this rank's f32 logits
+ * sampled token of every sequence (greedy argmax, or nvllm_sample when any temperature != 0; the row seed of
+ * sequence s at length n is mix64(sampling_seed ^ mix64(s * 0x9E3779B97F4A7C15 + n))) to h_tokens[num_seqs].  h_logits (nullable): this rank's f32 logits
  * [num_seqs, vocab/tp] copied back for parity tests. Synchronises the runner's stream before returning. */
 int nvllm_runner_execute(nvllm_runner* r, const nvllm_batch* batch, int64_t* h_tokens, float* h_logits);
 /* Same step split in two, for device-side timing: enqueue (no sync) / wait + fetch tokens. */

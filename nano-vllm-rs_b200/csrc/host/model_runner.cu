@@ -96,6 +96,9 @@ struct nvllm_runner {
   uint8_t *d_meta = nullptr, *h_meta = nullptr;
   size_t meta_bytes = 0;
   int64_t* h_tokens = nullptr;  // pinned
+  // sampler parameters of the current step (only used when some sequence has temperature != 0):
+  // [temperature f32 | top_k i32 | top_p f32 | row_seed u64] x max_seqs, pinned staging + device copy
+  uint8_t *d_samp = nullptr, *h_samp = nullptr;
   // pointers into d_meta for the current step
   int64_t *d_ids = nullptr, *d_pos = nullptr;
   int32_t *d_slots = nullptr, *d_cu_q = nullptr, *d_cu_k = nullptr, *d_ctx = nullptr, *d_tables = nullptr;
@@ -115,6 +118,7 @@ struct nvllm_runner {
     for (void* p : allocs) cudaFree(p);
     if (h_meta) cudaFreeHost(h_meta);
     if (h_tokens) cudaFreeHost(h_tokens);
+    if (h_samp) cudaFreeHost(h_samp);
     if (stream) cudaStreamDestroy(stream);
   }
 
@@ -139,6 +143,7 @@ struct nvllm_runner {
   int forward(int n_tokens, int n_seqs, bool is_prefill, bool paged_prefill, const nvllm_batch& b);
   int execute_async(const nvllm_batch& b);
   int fetch(int64_t* out, int n);
+  int sample(const nvllm_batch& b);
 };
 
 // ------------------------------------------------------------------------------------------------ create
@@ -242,6 +247,8 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   RUN(dalloc(&d_meta, meta_bytes));
   NVLLM_CUDA(cudaMallocHost(reinterpret_cast<void**>(&h_meta), meta_bytes));
   NVLLM_CUDA(cudaMallocHost(reinterpret_cast<void**>(&h_tokens), sizeof(int64_t) * S));
+  RUN(dalloc(&d_samp, 24 * S));
+  NVLLM_CUDA(cudaMallocHost(reinterpret_cast<void**>(&h_samp), 24 * S));
   NVLLM_CUDA(cudaStreamSynchronize(stream));
   return 0;
 }
@@ -487,10 +494,11 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
 int nvllm_runner::execute_async(const nvllm_batch& b) {
   NVLLM_CHECK_ARG(weights_ready, NVLLM_ERR_STATE, "execute: weights not initialised (init_weights / load_weight)");
   NVLLM_CHECK_ARG(b.num_seqs > 0 && b.num_tokens > 0, NVLLM_ERR_ARG, "execute: empty batch");
-  for (int i = 0; i < b.num_seqs; ++i)
-    NVLLM_CHECK_ARG(b.temperatures == nullptr || b.temperatures[i] == 0.0f, NVLLM_ERR_STATE,
-                    "execute: only greedy sampling (temperature == 0) runs on the device in this build (seq %d has %g)", i,
-                    b.temperatures[i]);
+  bool sampled = false;
+  for (int i = 0; i < b.num_seqs && b.temperatures != nullptr; ++i) sampled |= b.temperatures[i] != 0.0f;
+  // Under TP the logits are vocab-sharded and only the (max, id) combine of greedy decoding is wired across ranks.
+  NVLLM_CHECK_ARG(!sampled || tp == 1, NVLLM_ERR_STATE,
+                  "execute: temperature != 0 needs tensor_parallel_size == 1 (only greedy sampling is wired under TP)");
   if (b.is_prefill) {
     RUN(upload(b, 0));
     RUN(forward(b.num_tokens, b.num_seqs, true, b.has_block_tables != 0, b));
@@ -522,8 +530,39 @@ int nvllm_runner::execute_async(const nvllm_batch& b) {
       last_launches = g.nodes;
     }
   }
+  if (sampled) RUN(sample(b));  // overwrites the greedy tokens of the forward (outside the decode graph)
   NVLLM_CUDA(cudaMemcpyAsync(h_tokens, tokens, sizeof(int64_t) * b.num_seqs, cudaMemcpyDeviceToHost, stream));
   return 0;
+}
+
+// ModelRunner::sample_tokens -> Sampler::batch_sample (model_runner.rs:131-156, sampler.rs:221-254): the per-sequence
+// parameters travel as four small arrays in one H2D copy; one kernel samples the whole batch from the f32 logits.
+int nvllm_runner::sample(const nvllm_batch& b) {
+  const size_t S = static_cast<size_t>(max_seqs), n = static_cast<size_t>(b.num_seqs);
+  float* t = reinterpret_cast<float*>(h_samp);
+  int32_t* k = reinterpret_cast<int32_t*>(h_samp + 4 * S);
+  float* p = reinterpret_cast<float*>(h_samp + 8 * S);
+  uint64_t* sd = reinterpret_cast<uint64_t*>(h_samp + 16 * S);
+  auto mix = [](uint64_t x) {
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
+    x ^= x >> 27; x *= 0x94D049BB133111EBull;
+    x ^= x >> 31;
+    return x;
+  };
+  const uint64_t es = static_cast<uint64_t>(static_cast<int64_t>(cfg.sampling_seed));
+  for (size_t i = 0; i < n; ++i) {
+    t[i] = b.temperatures[i];
+    k[i] = b.top_k ? b.top_k[i] : 0;
+    p[i] = b.top_p ? b.top_p[i] : 0.0f;
+    const int64_t len = b.is_prefill ? b.cu_seqlens_k[i + 1] - b.cu_seqlens_k[i] : b.context_lens[i];
+    const uint64_t sid = b.seq_ids ? static_cast<uint64_t>(b.seq_ids[i]) : i;
+    sd[i] = mix(es ^ mix(sid * 0x9E3779B97F4A7C15ull + static_cast<uint64_t>(len)));
+  }
+  NVLLM_CUDA(cudaMemcpyAsync(d_samp, h_samp, 24 * S, cudaMemcpyHostToDevice, stream));
+  ++last_launches;
+  return nvllm_sample(tokens, logits, b.num_seqs, vshard, vshard, reinterpret_cast<const float*>(d_samp),
+                      reinterpret_cast<const int32_t*>(d_samp + 4 * S), reinterpret_cast<const float*>(d_samp + 8 * S),
+                      reinterpret_cast<const uint64_t*>(d_samp + 16 * S), nullptr, nullptr, stream);
 }
 
 int nvllm_runner::fetch(int64_t* out, int n) {

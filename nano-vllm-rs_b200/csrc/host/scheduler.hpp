@@ -13,7 +13,8 @@ namespace host {
 struct BatchArrays {
   std::vector<int64_t> seq_ids, input_ids, positions;
   std::vector<int32_t> slot_mapping, cu_q, cu_k, context_lens, block_tables;
-  std::vector<float> temperatures;
+  std::vector<float> temperatures, top_p;
+  std::vector<int32_t> top_k;
   std::vector<int32_t> seq_index;  // slab indices of the scheduled sequences (postprocess order)
 };
 
@@ -143,16 +144,21 @@ class Scheduler {
     BatchArrays& a = arrays_;
     const int32_t n = static_cast<int32_t>(a.seq_index.size());
     a.seq_ids.resize(n);
-    a.temperatures.resize(n);
-    for (int32_t i = 0; i < n; ++i) {
-      a.seq_ids[i] = seqs_[a.seq_index[i]].seq_id;
-      a.temperatures[i] = seqs_[a.seq_index[i]].sp.temperature;
+    a.temperatures.resize(n); a.top_k.resize(n); a.top_p.resize(n);
+    for (int32_t i = 0; i < n; ++i) {                                                         // model_runner.rs:137-146
+      const Sequence& s = seqs_[a.seq_index[i]];
+      a.seq_ids[i] = s.seq_id;
+      a.temperatures[i] = s.sp.temperature;
+      a.top_k[i] = s.sp.top_k;
+      a.top_p[i] = s.sp.top_p;
     }
     std::memset(out, 0, sizeof(*out));
     out->is_prefill = is_prefill ? 1 : 0;
     out->num_seqs = n;
     out->seq_ids = a.seq_ids.data();
     out->temperatures = a.temperatures.data();
+    out->top_k = a.top_k.data();
+    out->top_p = a.top_p.data();
   }
 
   void fill_tables(nvllm_batch* out) {                                                        // model_runner.rs:280-293

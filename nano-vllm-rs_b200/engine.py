@@ -21,7 +21,7 @@ class CConfig(C.Structure):
                 ("vocab_size", i32), ("hidden_size", i32), ("intermediate_size", i32), ("num_hidden_layers", i32),
                 ("num_attention_heads", i32), ("num_key_value_heads", i32), ("head_dim", i32),
                 ("max_position_embeddings", i32), ("tie_word_embeddings", i32), ("qk_norm", i32),
-                ("kv_layout", i32), ("reserved", i32), ("rms_norm_eps", f32), ("reserved_f", f32), ("rope_theta", f64)]
+                ("kv_layout", i32), ("sampling_seed", i32), ("rms_norm_eps", f32), ("reserved_f", f32), ("rope_theta", f64)]
 
 
 class CSamplingParams(C.Structure):
@@ -36,7 +36,8 @@ class CBatch(C.Structure):
                 ("max_seqlen_k", i32), ("max_blocks", i32), ("has_block_tables", i32), ("reserved", i32),
                 ("seq_ids", C.POINTER(i64)), ("input_ids", C.POINTER(i64)), ("positions", C.POINTER(i64)),
                 ("slot_mapping", C.POINTER(i32)), ("cu_seqlens_q", C.POINTER(i32)), ("cu_seqlens_k", C.POINTER(i32)),
-                ("context_lens", C.POINTER(i32)), ("block_tables", C.POINTER(i32)), ("temperatures", C.POINTER(f32))]
+                ("context_lens", C.POINTER(i32)), ("block_tables", C.POINTER(i32)), ("temperatures", C.POINTER(f32)),
+                ("top_k", C.POINTER(i32)), ("top_p", C.POINTER(f32))]
 
 
 class CSchedStats(C.Structure):
@@ -181,6 +182,13 @@ class Batch:
         self.context_lens = None if cb.is_prefill else arr(cb.context_lens, n, np.int32)
         self.block_tables = (arr(cb.block_tables, n * cb.max_blocks, np.int32).reshape(n, cb.max_blocks)
                              if cb.has_block_tables else None)
+        self.temperatures = arr(cb.temperatures, n, np.float32)
+        self.top_k = arr(cb.top_k, n, np.int32)
+        self.top_p = arr(cb.top_p, n, np.float32)
+
+    def seq_lens(self):
+        """Tokens of every scheduled sequence (prompt + completion so far): the `n` of the sampler's row seed."""
+        return np.diff(self.cu_seqlens_k).astype(np.int64) if self.is_prefill else self.context_lens.astype(np.int64)
 
 
 class Scheduler:
@@ -277,7 +285,7 @@ class ModelRunner:
         check(lib().nvllm_runner_load_weight(self.h, name.encode(), a.ctypes.data, rows, cols))
 
     def execute_model(self, batch: Batch, return_logits=False):
-        """execute_model + sample_tokens (model_runner.rs:105-156): returns greedy token ids [num_seqs] (and logits)."""
+        """execute_model + sample_tokens (model_runner.rs:105-156): returns the sampled token ids [num_seqs] (and logits)."""
         n = batch.c.num_seqs
         toks = np.zeros(n, np.int64)
         logits = np.zeros((n, self.vshard), np.float32) if return_logits else None
