@@ -1,57 +1,12 @@
-//! `extern "C"` declarations for include/nvllm.h + the safe wrappers with the reference's method signatures.
+//! Safe wrappers with the reference's method signatures over the generated `extern "C"` surface (ffi_gen.rs).
 //! COMPILE-UNVERIFIED (no Rust toolchain in the build image); the same ABI is exercised through ctypes by
 //! nano-vllm-rs_b200/_ffi.py and every test under tests/.
-#![allow(non_camel_case_types)]
-use std::ffi::{c_char, c_void, CStr};
+use std::ffi::{c_void, CStr};
 
-#[repr(C)]
-#[derive(Clone, Copy, Debug)]
-pub struct nvllm_kv_layout {
-    pub block_size: i32,
-    pub num_kv_heads: i32,
-    pub head_dim: i32,
-    pub reserved: i32,
-    pub block_stride: i64,
-    pub token_stride: i64,
-    pub head_stride: i64,
-}
+pub use crate::ffi_gen::*; // every extern "C" declaration + #[repr(C)] struct of include/nvllm.h and nvllm_engine.h
 
 pub const NVLLM_BF16: i32 = 0;
 pub const NVLLM_F32: i32 = 1;
-
-extern "C" {
-    pub fn nvllm_version() -> i32;
-    pub fn nvllm_last_error() -> *const c_char;
-    pub fn nvllm_store_kvcache(k: *const c_void, v: *const c_void, k_cache: *mut c_void, v_cache: *mut c_void,
-                               slot_mapping: *const i32, num_tokens: i32, kv_token_stride: i64,
-                               layout: *const nvllm_kv_layout, dtype: i32, stream: *mut c_void) -> i32;
-    pub fn nvllm_paged_decode_workspace_bytes(batch: i32, num_heads: i32, head_dim: i32, num_splits: i32) -> usize;
-    pub fn nvllm_paged_decode_attention(out: *mut c_void, q: *const c_void, k_cache: *const c_void, v_cache: *const c_void,
-                                        block_tables: *const i32, context_lens: *const i32, batch: i32, num_heads: i32,
-                                        max_blocks_per_seq: i32, q_token_stride: i64, out_token_stride: i64,
-                                        layout: *const nvllm_kv_layout, scale: f32, workspace: *mut c_void,
-                                        workspace_bytes: usize, num_splits: i32, dtype: i32, stream: *mut c_void) -> i32;
-    pub fn nvllm_varlen_prefill_attention(out: *mut c_void, q: *const c_void, k: *const c_void, v: *const c_void,
-                                          cu_seqlens_q: *const i32, cu_seqlens_k: *const i32, batch: i32, total_q: i32,
-                                          total_k: i32, max_seqlen_q: i32, max_seqlen_k: i32, num_heads: i32,
-                                          num_kv_heads: i32, head_dim: i32, q_token_stride: i64, kv_token_stride: i64,
-                                          out_token_stride: i64, k_cache: *const c_void, v_cache: *const c_void,
-                                          block_tables: *const i32, max_blocks_per_seq: i32,
-                                          layout: *const nvllm_kv_layout, scale: f32, dtype: i32, stream: *mut c_void) -> i32;
-    pub fn nvllm_gemm_bf16(y: *mut c_void, x: *const c_void, w: *const c_void, m: i32, n: i32, k: i32, ldx: i64, ldw: i64,
-                           ldy: i64, out_dtype: i32, workspace: *mut c_void, workspace_bytes: usize, stream: *mut c_void) -> i32;
-    pub fn nvllm_add_rmsnorm(out: *mut c_void, x: *const c_void, residual: *mut c_void, weight: *const c_void,
-                             num_tokens: i32, hidden: i32, eps: f32, dtype: i32, stream: *mut c_void) -> i32;
-    pub fn nvllm_qknorm_rope_store(qkv: *mut c_void, positions: *const i64, cos_sin: *const f32, q_norm_w: *const c_void,
-                                   k_norm_w: *const c_void, eps: f32, num_tokens: i32, num_heads: i32, num_kv_heads: i32,
-                                   head_dim: i32, max_position: i32, k_cache: *mut c_void, v_cache: *mut c_void,
-                                   slot_mapping: *const i32, layout: *const nvllm_kv_layout, dtype: i32,
-                                   stream: *mut c_void) -> i32;
-    pub fn nvllm_silu_mul(out: *mut c_void, x: *const c_void, num_tokens: i32, inter: i32, dtype: i32, stream: *mut c_void) -> i32;
-    pub fn nvllm_argmax(out_ids: *mut i64, out_max: *mut f32, logits: *const c_void, batch: i32, vocab: i32, ld: i64,
-                        vocab_offset: i64, logits_dtype: i32, stream: *mut c_void) -> i32;
-    // ... the remaining entry points of nvllm.h / nvllm_engine.h follow the same pattern.
-}
 
 /// Non-zero return -> anyhow::Error carrying nvllm_last_error() (the reference's `map_err(anyhow!)` convention,
 /// model_runner.rs:123-124).
@@ -87,5 +42,20 @@ impl DecodeAttention {
         check(nvllm_paged_decode_attention(out, q, k_cache, v_cache, block_tables, context_lens, batch, self.num_heads,
                                            max_blocks, self.num_heads as i64 * d, self.num_heads as i64 * d, &self.layout,
                                            self.scale, workspace, workspace_bytes, 0, NVLLM_BF16, stream))
+    }
+}
+
+/// What `ModelRunner::sample_tokens` -> `Sampler::batch_sample` (src/engine/model_runner.rs:131-156,
+/// src/layers/sampler.rs:221-254) becomes: the per-sequence parameters are device arrays, one launch samples the batch.
+pub struct DeviceSampler;
+
+impl DeviceSampler {
+    /// logits: f32 [batch, vocab] on the device; temperatures / top_k / top_p / row_seeds: device arrays of `batch`
+    /// entries (top_k / top_p may be null = None for every row); out_ids: i64 [batch] on the device.
+    #[allow(clippy::too_many_arguments)]
+    pub unsafe fn forward(out_ids: *mut i64, logits: *const f32, batch: i32, vocab: i32, temperatures: *const f32,
+                          top_k: *const i32, top_p: *const f32, row_seeds: *const u64, stream: *mut c_void) -> anyhow::Result<()> {
+        check(nvllm_sample(out_ids, logits, batch, vocab, vocab as i64, temperatures, top_k, top_p, row_seeds,
+                           std::ptr::null_mut(), std::ptr::null_mut(), stream))
     }
 }
