@@ -298,7 +298,7 @@ def main():
         "config": {"workload": f"{model} bf16 decode: {B} concurrent seqs, paged KV block 256, "
                                f"{wl['prompt']}-token prompts + {wl['decode']} decode steps; timed steps at context "
                                f"{ctx_first}..{ctx_last} (workload mean {wl['prompt'] + wl['decode'] // 2})",
-                   "model": model, "seqs": B, "prompt_len_used": prompt, "parallelism": f"tp{world}",
+                   "seqs": B, "prompt_len_used": prompt, "parallelism": f"tp{world}",
                    "cuda_graphs": not args.eager, "l2_note": "inputs larger than L2: one step reads "
                    f"{round(att_bytes * layers / 1e9, 1)} GB of KV (L2 = 126 MB), no flush needed",
                    "prefill_steps_untimed": n_prefill, "prefill_s": round(prefill_s, 2)},

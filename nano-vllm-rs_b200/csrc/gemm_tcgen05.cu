@@ -86,9 +86,8 @@ template <int BN, typename OutT, bool SILU, int CN, bool ROPE = false>
 __global__ void __launch_bounds__(256, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles,
-                    const RopeEpi re = RopeEpi{}) {
-  using C = GemmCfg<BN>;
-  constexpr int STAGES = C::kStages;
+                    const RopeEpi re = RopeEpi{}, int STAGES = GemmCfg<BN>::kStages) {
+  using C = GemmCfg<BN>;  // STAGES <= C::kStages: ring depth of this launch (fewer stages -> two CTAs per SM, see launch_gemm)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B tiles: 1024-byte aligned
   const uint32_t sA = smem_base;
@@ -336,9 +335,19 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
   const int num_tiles = num_m_tiles * (num_n_tiles / CN);  // cluster tiles (the caller guarantees num_n_tiles % CN == 0)
   const int max_clusters = sm_count() / CN;
   const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+  // Ring depth: NVLLM_GEMM_STAGES (benchmark knob) caps it for single-wave (decode-sized) launches: with <= ~100 KB of
+  // shared memory two CTAs fit on an SM, so the NEXT kernel's CTAs become resident (prologue + weight prefetch under PDL)
+  // while this kernel's are still running.
+  int stages = C::kStages;
+  if (CN == 1 && num_tiles <= max_clusters) {
+    const char* e = getenv("NVLLM_GEMM_STAGES");
+    const int want = e ? atoi(e) : 0;
+    if (want >= 2 && want < stages) stages = want;
+  }
+  const int smem = C::kSmemBytes - (C::kStages - stages) * C::kStageBytes;
   if constexpr (CN == 1) {
-    NVLLM_CUDA(launch_pdl(kern, dim3(clusters), dim3(256), C::kSmemBytes, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
-                          num_m_tiles, num_tiles, re));
+    NVLLM_CUDA(launch_pdl(kern, dim3(clusters), dim3(256), smem, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
+                          num_m_tiles, num_tiles, re, stages));
   } else {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(clusters * CN);
@@ -352,7 +361,8 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles, re));
+    NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles, re,
+                                  static_cast<int>(C::kStages)));
   }
   return 0;
 }
@@ -392,9 +402,14 @@ static bool use_2cta();
 // from L2 once per n-tile and also do better on single-CTA tiles until a split-K variant exists.
 static bool want_2cta(int m, int n, int k) {
   if (m <= 128 || !use_2cta()) return false;
-  const long big_tiles = static_cast<long>((m + 255) / 256) * ((n + 255) / 256);
-  if (m < 512 && big_tiles < sm_count() / 2) return false;
-  if (m <= 512 && k > 2 * n) return false;
+  {
+    const char* e = getenv("NVLLM_GEMM_2CTA");  // "2": benchmark knob, CTA pairs for every m > 128
+    if (e && e[0] == '2') return true;
+  }
+  // In-graph measurements (profiles/r01_gemm_ingraph_v2_splitk.jsonl): at M = 512 (the TP decode batches) the single-CTA
+  // kernel is 7-17 % faster on all four projections; CTA pairs pay off from two 256-row tile rows upwards (prefill).
+  if (m <= 512) return false;
+  (void)n; (void)k;
   return true;
 }
 

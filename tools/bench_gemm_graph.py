@@ -19,11 +19,11 @@ SHAPES = {  # name: (M, N, K, kind)
     "8B/tp8 qkv": (512, 768, 4096, "gemm"), "8B/tp8 o": (512, 4096, 512, "gemm"), "8B/tp8 gate_up+silu": (512, 1536, 4096, "silu"),
     "8B/tp8 down": (512, 4096, 1536, "gemm"),
 }
-KNOBS = [{}, {"NVLLM_GEMM_SPLITK": "0"}, {"NVLLM_GEMM_SPLITK": "64,4"}, {"NVLLM_GEMM_SPLITK": "128,2"},
-         {"NVLLM_GEMM_SPLITK": "128,4"}, {"NVLLM_GEMM_SPLITK": "128,8"}, {"NVLLM_GEMM_SPLITK": "256,2"},
-         {"NVLLM_GEMM_SPLITK": "256,4"}, {"NVLLM_GEMM_SPLITK": "256,8"}, {"NVLLM_GEMM_SPLITK": "0", "NVLLM_GEMM_MCAST": "0"},
-         {"NVLLM_GEMM_SPLITK": "0", "NVLLM_GEMM_2CTA": "0"}]
-ALL = ("NVLLM_GEMM_BN", "NVLLM_GEMM_MCAST", "NVLLM_GEMM_2CTA", "NVLLM_GEMM_SPLITK")
+S, T, G = "NVLLM_GEMM_SPLITK", "NVLLM_GEMM_SK_STAGES", "NVLLM_GEMM_STAGES"
+KNOBS = [{}, {S: "0"}, {S: "64,4"}, {S: "64,4", T: "3"}, {S: "64,4", T: "8"}, {S: "64,2"}, {S: "128,4"}, {S: "128,4", T: "3"},
+         {S: "128,2", T: "3"}, {S: "128,8"}, {S: "256,4", T: "3"}, {S: "256,2", T: "3"},
+         {S: "0", G: "3"}, {S: "0", G: "4"}, {S: "0", "NVLLM_GEMM_2CTA": "2"}, {S: "0", "NVLLM_GEMM_BN": "128"}]
+ALL = ("NVLLM_GEMM_BN", "NVLLM_GEMM_MCAST", "NVLLM_GEMM_2CTA", S, T, G)
 
 
 def run(name, M, N, K, kind, layers, reps):
