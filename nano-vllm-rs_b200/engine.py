@@ -308,13 +308,31 @@ class ModelRunner:
         return ms.value, nbytes.value
 
 
-class LLMEngine:
-    """LLMEngine (llm_engine.rs:23-362), synchronous: add_request / step / generate over token ids.
-    (Tokeniser, async streaming and stats facade are out of scope for the hot path — SURVEY.md §8f #4.)"""
+@dataclass
+class SequenceOutput:
+    """SequenceOutput (sequence.rs:30-46)."""
+    seq_id: int
+    text: str
+    token_ids: List[int]
+    completion_token_ids: List[int]
+    num_prompt_tokens: int
+    num_completion_tokens: int
+    status: str
 
-    def __init__(self, config: Config, comm=None, seed=1234, std=0.02, init_weights=True):
+
+class LLMEngine:
+    """LLMEngine (llm_engine.rs:23-362), synchronous: add_request / step / generate / generate_stream / get_stats /
+    health_check / shutdown over token ids.  `tokenizer` (optional): any object with encode(str) -> ids (list or an object
+    with .ids, as the HF `tokenizers` crate the reference binds, llm_engine.rs:200-230) and decode(ids) -> str; with it,
+    prompts may be strings and SequenceOutput.text is filled.  The reference's tokio plumbing (Arc<Mutex<..>>, mpsc
+    channel, spawn) has no counterpart: one caller thread drives the engine, streaming is a Python generator."""
+
+    def __init__(self, config: Config, comm=None, seed=1234, std=0.02, init_weights=True, tokenizer=None):
         config.validate()
         self.config = config
+        self.tokenizer = tokenizer
+        self.is_running = True
+        self._live = {}     # seq_id -> tokens already reported (for step outputs / streaming)
         h = vp()
         check(lib().nvllm_engine_create(C.byref(h), C.byref(config.c), comm))
         self.h = h
@@ -328,8 +346,24 @@ class LLMEngine:
             lib().nvllm_engine_destroy(self.h)
             self.h = None
 
-    def add_request(self, prompt_token_ids, sampling_params: SamplingParams = None) -> int:
-        return self.scheduler.add_sequence(prompt_token_ids, sampling_params)
+    # ---- tokenisation (llm_engine.rs:200-230: create_sequences) ----
+    def _encode(self, prompt):
+        if isinstance(prompt, str):
+            if self.tokenizer is None:
+                raise ValueError("string prompt given but the engine has no tokenizer")
+            enc = self.tokenizer.encode(prompt)
+            return list(getattr(enc, "ids", enc))
+        return list(prompt)
+
+    def _decode(self, ids):
+        return self.tokenizer.decode(list(ids)) if self.tokenizer is not None else ""
+
+    def add_request(self, prompt, sampling_params: SamplingParams = None) -> int:
+        if not self.is_running:
+            raise RuntimeError("engine has been shut down")
+        sid = self.scheduler.add_sequence(self._encode(prompt), sampling_params)
+        self._live[sid] = None
+        return sid
 
     def step(self):
         """LLMEngine::step (llm_engine.rs:155-197). Returns (is_prefill, num_seqs, num_tokens)."""
@@ -340,16 +374,78 @@ class LLMEngine:
     def is_finished(self):
         return bool(lib().nvllm_engine_is_finished(self.h))
 
-    def generate(self, prompts: List[List[int]], sampling_params: SamplingParams = None):
-        """LLMEngine::generate (llm_engine.rs:71-98) over token-id prompts; returns completion token ids per prompt."""
+    def _output(self, sid, s):
+        n = s["num_prompt_tokens"]
+        comp = s["token_ids"][n:]
+        return SequenceOutput(sid, self._decode(comp), s["token_ids"], comp, n, len(comp), s["status"])
+
+    def step_outputs(self) -> List[SequenceOutput]:
+        """One step with the reference's return value (llm_engine.rs:155-197): outputs of the sequences that FINISHED in it."""
+        self.step()
+        done = []
+        for sid in list(self._live):
+            s = self.scheduler.sequence(sid)
+            if s["status"] == "Finished":
+                done.append(self._output(sid, s))
+                del self._live[sid]
+        return done
+
+    def generate(self, prompts, sampling_params: SamplingParams = None):
+        """LLMEngine::generate (llm_engine.rs:71-98): completion token ids per prompt, in prompt order."""
         ids = [self.add_request(p, sampling_params) for p in prompts]
         while not self.is_finished():
             self.step()
         out = []
         for i in ids:
             s = self.scheduler.sequence(i)
+            self._live.pop(i, None)
             out.append(s["token_ids"][s["num_prompt_tokens"]:])
         return out
+
+    def generate_outputs(self, prompts, sampling_params: SamplingParams = None) -> List[SequenceOutput]:
+        """generate with the reference's return type (Vec<SequenceOutput>, in prompt order)."""
+        ids = [self.add_request(p, sampling_params) for p in prompts]
+        while not self.is_finished():
+            self.step()
+        for i in ids:
+            self._live.pop(i, None)
+        return [self._output(i, self.scheduler.sequence(i)) for i in ids]
+
+    def generate_stream(self, prompts, sampling_params: SamplingParams = None):
+        """LLMEngine::generate_stream (llm_engine.rs:101-128) as a generator: after every step yields one SequenceOutput per
+        sequence that produced a token in it (cumulative completion so far; status "Finished" on the last one)."""
+        ids = [self.add_request(p, sampling_params) for p in prompts]
+        seen = {i: 0 for i in ids}
+        while seen:
+            self.step()
+            for i in list(seen):
+                s = self.scheduler.sequence(i)
+                n = len(s["token_ids"]) - s["num_prompt_tokens"]
+                if n > seen[i] or s["status"] == "Finished":
+                    yield self._output(i, s)
+                seen[i] = n
+                if s["status"] == "Finished":
+                    del seen[i]
+                    self._live.pop(i, None)
+
+    def get_stats(self):
+        """EngineStats (llm_engine.rs:312-327,375-400): scheduler counters + block-memory utilisation (percent)."""
+        st = self.scheduler.get_stats()
+        total = max(1, st["total_blocks"])
+        return {"scheduler": st,
+                "memory": {"total_blocks": st["total_blocks"], "free_blocks": st["free_blocks"], "used_blocks": st["used_blocks"],
+                           "utilization": 100.0 * st["used_blocks"] / total},
+                "is_running": self.is_running}
+
+    def health_check(self):
+        """HealthStatus (llm_engine.rs:330-342,404-416): healthy while block utilisation is below 95 %."""
+        st = self.get_stats()
+        return {"is_healthy": st["memory"]["utilization"] < 95.0, "memory_pressure": st["memory"]["utilization"],
+                "active_sequences": st["scheduler"]["running"], "waiting_sequences": st["scheduler"]["waiting"]}
+
+    def shutdown(self):
+        """LLMEngine::shutdown (llm_engine.rs:345-357): stop accepting requests (queued work is dropped with the engine)."""
+        self.is_running = False
 
 
 class LLMEngineBuilder:

@@ -164,3 +164,53 @@ def test_cfg1_qwen3_0_6b_4x128_prompts_64_decode_steps(cuda):
     print(stats)
     assert stats["prefill_steps"] == 1 and stats["decode_steps"] == 64 and stats["rows"] == 4 * 65
     assert stats["strict"] >= 0.9 * stats["rows"]
+
+
+class _ByteTokenizer:
+    """Stand-in for the HF tokenizer the reference binds (llm_engine.rs:200-230): bytes <-> ids below 256."""
+    def encode(self, text):
+        return list(text.encode("utf-8"))
+
+    def decode(self, ids):
+        return bytes(int(i) % 256 for i in ids).decode("latin-1")
+
+
+def test_engine_facade_stream_outputs_stats(cuda):
+    """generate_outputs / generate_stream / step_outputs / get_stats / health_check / shutdown (llm_engine.rs:71-357)."""
+    from nano_vllm_rs_b200 import engine as E
+    cfg = E.Config("tiny", kvcache_block_size=16, num_kvcache_blocks=64)
+    sp = E.SamplingParams(temperature=0.0, max_tokens=12, ignore_eos=True)
+    prompts = ["paged attention", "b200", "the quick brown fox jumps over the lazy dog"]
+    eng = E.LLMEngine(cfg, std=0.05, tokenizer=_ByteTokenizer())
+    outs = eng.generate_outputs(prompts, sp)
+    assert [o.num_prompt_tokens for o in outs] == [len(p.encode()) for p in prompts]
+    assert all(o.num_completion_tokens == 12 and o.status == "Finished" and len(o.text) == 12 for o in outs)
+    assert all(o.token_ids[:o.num_prompt_tokens] == list(p.encode()) for o, p in zip(outs, prompts))
+    # streaming yields every token once, cumulatively, and ends with the same completions
+    eng2 = E.LLMEngine(cfg, std=0.05, tokenizer=_ByteTokenizer())
+    last, counts = {}, {}
+    for o in eng2.generate_stream(prompts, sp):
+        assert o.num_completion_tokens == counts.get(o.seq_id, 0) + 1
+        counts[o.seq_id] = o.num_completion_tokens
+        last[o.seq_id] = o
+    assert [last[i].completion_token_ids for i in sorted(last)] == [o.completion_token_ids for o in outs]
+    assert all(o.status == "Finished" for o in last.values())
+    # step_outputs returns sequences as they finish (different max_tokens -> different steps)
+    eng3 = E.LLMEngine(cfg, std=0.05)
+    a = eng3.add_request([1, 2, 3], E.SamplingParams(temperature=0.0, max_tokens=3, ignore_eos=True))
+    b = eng3.add_request([4, 5, 6, 7], E.SamplingParams(temperature=0.0, max_tokens=6, ignore_eos=True))
+    order = []
+    st_mid = None
+    while not eng3.is_finished():
+        order += [o.seq_id for o in eng3.step_outputs()]
+        st_mid = st_mid or eng3.get_stats()
+    assert order == [a, b]
+    assert st_mid["memory"]["used_blocks"] == 2 and 0 < st_mid["memory"]["utilization"] < 100 and st_mid["is_running"]
+    end = eng3.get_stats()
+    assert end["scheduler"]["finished"] == 2 and end["memory"]["used_blocks"] == 0
+    assert eng3.health_check() == {"is_healthy": True, "memory_pressure": 0.0, "active_sequences": 0, "waiting_sequences": 0}
+    eng3.shutdown()
+    with pytest.raises(RuntimeError):
+        eng3.add_request([1])
+    with pytest.raises(ValueError):
+        E.LLMEngine(cfg, std=0.05).add_request("needs a tokenizer")

@@ -85,9 +85,11 @@ def test_gemm_strided_views(cuda):
 
 
 @pytest.mark.parametrize("m,inter,k", [(256, 3072, 1024), (300, 1536, 512), (512, 12288, 4096), (64, 3072, 1024), (129, 256, 128)])
-def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k):
-    """gate_up GEMM with the SiLU*mul epilogue (M > 128: CTA-pair kernel) is bit-identical to GEMM + silu_mul."""
+def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k, monkeypatch):
+    """gate_up GEMM with the SiLU*mul epilogue (M > 128: CTA-pair kernel) is bit-identical to GEMM + silu_mul
+    (split-K off: it changes the summation order, and is compared against the oracle in its own tests)."""
     from nano_vllm_rs_b200 import ops
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", "0")
     g = torch.Generator(device="cuda").manual_seed(m + inter + k)
     x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
     w = (torch.randn((2 * inter, k), generator=g, device=cuda) * 0.05).to(torch.bfloat16)
@@ -102,10 +104,11 @@ def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k):
 
 @pytest.mark.parametrize("kind", ["reference", "head_major"])
 @pytest.mark.parametrize("m,H,Hkv,k,qknorm", [(256, 16, 8, 1024, True), (37, 4, 1, 512, True), (130, 8, 2, 256, False)])
-def test_gemm_qkv_rope_store_fused_equals_unfused(cuda, kind, m, H, Hkv, k, qknorm):
+def test_gemm_qkv_rope_store_fused_equals_unfused(cuda, kind, m, H, Hkv, k, qknorm, monkeypatch):
     """qkv GEMM with the q/k-norm + RoPE + KV-store epilogue vs nvllm_gemm_bf16 followed by nvllm_qknorm_rope_store
-    (same rounding points), for both cache layouts."""
+    (same rounding points; split-K off so that both GEMMs sum in the same order), for both cache layouts."""
     from nano_vllm_rs_b200 import ops
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", "0")
     from nano_vllm_rs_b200._ffi import KvLayout
     D, bs = 128, 16
     g = torch.Generator(device="cuda").manual_seed(m + H + k)

@@ -58,7 +58,7 @@ def main():
     ap.add_argument("--only", default="")
     a = ap.parse_args()
     for name, (M, N, K, kind) in SHAPES.items():
-        if a.only and a.only not in name:
+        if a.only and not any(o in name for o in a.only.split(",")):
             continue
         for kn in KNOBS:
             for k in ALL:
