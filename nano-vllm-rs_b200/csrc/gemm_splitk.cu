@@ -24,14 +24,16 @@ struct SkCfg {
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kMaxStages = (192 * 1024) / kStageBytes > 8 ? 8 : (192 * 1024) / kStageBytes;
-  // f32 partial tile, row-major with 4 floats of padding per row: 16-byte accesses by 32 consecutive rows hit 8
-  // distinct 16-byte bank groups per quarter-warp (row pitch = BN*4 + 16 bytes), for the local stores and the DSMEM loads
-  static constexpr int kRowPitch = (BN + 4) * 4;
-  static constexpr int kPartialBytes = BM * kRowPitch;
+  // f32 partial tile, column-major [BN][128]: a warp (32 consecutive rows of one column) touches 128 contiguous bytes, for
+  // the local stores (conflict-free) and for the DSMEM loads (one coalesced request per warp — strided 16-byte DSMEM
+  // loads measured 2.4 us slower per kernel, profiles/r01_gemm_ingraph_v3_splitk_v2.jsonl)
+  static constexpr int kColPitch = BM * 4;
+  static constexpr int kPartialBytes = BN * kColPitch;
   static constexpr int kTmemCols = BN < 32 ? 32 : BN;
   static constexpr int kMaxBars = 2 * kMaxStages + 1;
-  // The operand ring uses `stages` stages (a launch parameter: few stages -> ~100 KB -> two CTAs per SM, so the next
-  // kernel's prologue and weight prefetch overlap this kernel's tail); the partial tile is parked over the drained ring.
+  // The operand ring uses `stages` stages (a launch parameter; the k-loop is latency-bound, so the default is the deepest
+  // ring that fits: shallower rings that let two CTAs share an SM measured slower); the partial tile is parked over the
+  // drained ring.
   static constexpr int ring_bytes(int stages) {
     return stages * kStageBytes > kPartialBytes ? stages * kStageBytes : ((kPartialBytes + 1023) / 1024) * 1024;
   }
@@ -43,19 +45,19 @@ __device__ __forceinline__ uint32_t dsmem_addr(uint32_t local, uint32_t cta) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(local), "r"(cta));
   return r;
 }
-__device__ __forceinline__ float4 ld_dsmem_v4(uint32_t addr) {
-  float4 v;
-  asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];\n" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];\n" : "=f"(v) : "r"(addr) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_smem_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+__device__ __forceinline__ void st_smem_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;\n" ::"r"(addr), "f"(v) : "memory");
 }
 
 // One cluster of SK CTAs per (m_tile, n_tile); cluster rank r accumulates k-blocks [r * kb_per, (r + 1) * kb_per).
 // SILU: w = [gate (N rows) | up (N rows)], the B tile is BN/2 gate rows + the matching BN/2 up rows, y[:, BN/2 per tile].
 template <int BN, int SK, bool SILU>
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, 1)
 gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                    bf16* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int STAGES) {
   using C = SkCfg<BN>;
@@ -137,19 +139,19 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
   } else if (warp >= 4) {
-    // ===== park the partial tile: TMEM -> f32 shared memory, padded row-major, 16-byte stores =====
+    // ===== park the partial tile: TMEM -> f32 shared memory, column-major (lanes = rows: conflict-free) =====
     const int q = warp & 3;
     mbar_wait(tfull_bar, 0);  // every MMA has retired: the operand ring is dead and can be overwritten
     tc_fence_after();
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const uint32_t prow = smem_base + (q * 32 + lane) * C::kRowPitch;
+    const uint32_t prow = smem_base + (q * 32 + lane) * 4;
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(taddr + c * 32, r);
       tmem_ld_wait();
 #pragma unroll
-      for (int e = 0; e < 32; e += 4) st_smem_v4(prow + (c * 32 + e) * 4, r[e], r[e + 1], r[e + 2], r[e + 3]);
+      for (int e = 0; e < 32; ++e) st_smem_f32(prow + (c * 32 + e) * C::kColPitch, __uint_as_float(r[e]));
     }
     tc_fence_before();
   }
@@ -164,7 +166,7 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     const int row = m_tile * C::BM + row_in;
     uint32_t peer[SK];
 #pragma unroll
-    for (int r = 0; r < SK; ++r) peer[r] = dsmem_addr(smem_base + row_in * C::kRowPitch, static_cast<uint32_t>(r));
+    for (int r = 0; r < SK; ++r) peer[r] = dsmem_addr(smem_base + row_in * 4, static_cast<uint32_t>(r));
     if constexpr (SILU) {
       constexpr int CW = BN / (2 * SK);  // output columns of this CTA
       static_assert(CW >= 8 && CW % 8 == 0, "slice must be whole 16-byte vectors");
@@ -172,19 +174,21 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
 #pragma unroll 1
       for (int j = 0; j < CW; j += 8) {
         const int cg = rank * CW + j, cu = BN / 2 + cg;
-        float4 vg[SK][2], vu[SK][2];
+        float vg[SK][8], vu[SK][8];
 #pragma unroll
-        for (int r = 0; r < SK; ++r) {  // all loads of the chunk in flight before the first add
-          vg[r][0] = ld_dsmem_v4(peer[r] + cg * 4); vg[r][1] = ld_dsmem_v4(peer[r] + cg * 4 + 16);
-          vu[r][0] = ld_dsmem_v4(peer[r] + cu * 4); vu[r][1] = ld_dsmem_v4(peer[r] + cu * 4 + 16);
-        }
-        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, u[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int r = 0; r < SK; ++r)  // all 16 * SK loads of the chunk in flight before the first add
 #pragma unroll
-        for (int r = 0; r < SK; ++r) {  // fixed rank order
-          g[0] += vg[r][0].x; g[1] += vg[r][0].y; g[2] += vg[r][0].z; g[3] += vg[r][0].w;
-          g[4] += vg[r][1].x; g[5] += vg[r][1].y; g[6] += vg[r][1].z; g[7] += vg[r][1].w;
-          u[0] += vu[r][0].x; u[1] += vu[r][0].y; u[2] += vu[r][0].z; u[3] += vu[r][0].w;
-          u[4] += vu[r][1].x; u[5] += vu[r][1].y; u[6] += vu[r][1].z; u[7] += vu[r][1].w;
+          for (int e = 0; e < 8; ++e) {
+            vg[r][e] = ld_dsmem_f32(peer[r] + (cg + e) * C::kColPitch);
+            vu[r][e] = ld_dsmem_f32(peer[r] + (cu + e) * C::kColPitch);
+          }
+        float g[8], u[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float sg = 0.f, su = 0.f;
+#pragma unroll
+          for (int r = 0; r < SK; ++r) { sg += vg[r][e]; su += vu[r][e]; }  // fixed rank order
+          g[e] = sg; u[e] = su;
         }
         uint32_t o[4];
 #pragma unroll
@@ -200,25 +204,24 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     } else {
       constexpr int CW = BN / SK;
       static_assert(CW >= 8 && CW % 8 == 0, "slice must be whole 16-byte vectors");
-      constexpr int CH = (CW % 16 == 0 && SK <= 4) ? 16 : 8;  // columns per iteration (CH/4 * SK 16-byte loads in flight)
+      constexpr int CH = (CW % 16 == 0 && SK <= 4) ? 16 : 8;  // columns per iteration: CH * SK coalesced loads in flight
       bf16* dst = y + row * ldy + n_tile * BN + rank * CW;
 #pragma unroll 1
       for (int j = 0; j < CW; j += CH) {
         const int c0 = rank * CW + j;
-        float4 v[SK][CH / 4];
+        float v[SK][CH];
 #pragma unroll
         for (int r = 0; r < SK; ++r)
 #pragma unroll
-          for (int e = 0; e < CH / 4; ++e) v[r][e] = ld_dsmem_v4(peer[r] + (c0 + e * 4) * 4);
+          for (int e = 0; e < CH; ++e) v[r][e] = ld_dsmem_f32(peer[r] + (c0 + e) * C::kColPitch);
         float a[CH];
 #pragma unroll
-        for (int e = 0; e < CH; ++e) a[e] = 0.f;
+        for (int e = 0; e < CH; ++e) {
+          float sum = 0.f;
 #pragma unroll
-        for (int r = 0; r < SK; ++r)  // fixed rank order
-#pragma unroll
-          for (int e = 0; e < CH / 4; ++e) {
-            a[4 * e + 0] += v[r][e].x; a[4 * e + 1] += v[r][e].y; a[4 * e + 2] += v[r][e].z; a[4 * e + 3] += v[r][e].w;
-          }
+          for (int r = 0; r < SK; ++r) sum += v[r][e];  // fixed rank order
+          a[e] = sum;
+        }
         if (row < M) {
 #pragma unroll
           for (int e = 0; e < CH; e += 8)
@@ -236,12 +239,13 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   }
 }
 
-// Stages of the operand ring: NVLLM_GEMM_SK_STAGES (benchmark knob) or 4, never more than the k-blocks of one CTA.
+// Stages of the operand ring: NVLLM_GEMM_SK_STAGES (benchmark knob) or the deepest that fits, never more than the
+// k-blocks of one CTA.
 template <int BN>
 int splitk_stages(int kb_per) {
   using C = SkCfg<BN>;
   const char* e = getenv("NVLLM_GEMM_SK_STAGES");
-  int want = e ? atoi(e) : 4;
+  int want = e ? atoi(e) : C::kMaxStages;
   if (want < 2) want = 2;
   if (want > C::kMaxStages) want = C::kMaxStages;
   return want < kb_per ? want : (kb_per < 1 ? 1 : kb_per);
@@ -274,11 +278,13 @@ int launch_splitk(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, 
   return 0;
 }
 
-// Cost of one CTA in "bytes through the SM's TMA port": operands + park / reduce of the partial tile (~ one tile
-// written, one read back).  Clusters of 8 measured 3-6 us slower than clusters of 4 at equal bytes (fewer of them can
-// be co-scheduled per GPC), hence the flat penalty (profiles/r01_gemm_ingraph_v2_splitk.jsonl).
+// Cost of one CTA in "bytes through the SM's TMA port" (~40-60 B/clk): the operands, plus the reduce-scatter of the
+// partial tile over DSMEM — (SK-1)/SK of a BN x 128 f32 tile per CTA at ~20 B/clk (B300_MICROARCH.md: 17-21 B/clk), i.e.
+// weighted x4 — which is why narrow tiles with SK = 4 win for the 0.6B projections.  Clusters of 8 measured 3-6 us
+// slower than clusters of 4 at equal bytes (fewer can be co-scheduled per GPC): flat penalty.
+// Data: profiles/r01_gemm_ingraph_v2_splitk.jsonl, r01_gemm_ingraph_v3_splitk_v2.jsonl.
 long splitk_cost(int bn, int sk, int k) {
-  return 2l * (128 + bn) * (k / sk) + (sk > 1 ? 2l * bn * 512 : 0) + (sk >= 8 ? 600l * 1024 : 0);
+  return 2l * (128 + bn) * (k / sk) + (sk > 1 ? 4l * 512 * bn * (sk - 1) / sk : 0) + (sk >= 8 ? 600l * 1024 : 0);
 }
 
 }  // namespace

@@ -20,9 +20,8 @@ SHAPES = {  # name: (M, N, K, kind)
     "8B/tp8 down": (512, 4096, 1536, "gemm"),
 }
 S, T, G = "NVLLM_GEMM_SPLITK", "NVLLM_GEMM_SK_STAGES", "NVLLM_GEMM_STAGES"
-KNOBS = [{}, {S: "0"}, {S: "64,4"}, {S: "64,4", T: "3"}, {S: "64,4", T: "8"}, {S: "64,2"}, {S: "128,4"}, {S: "128,4", T: "3"},
-         {S: "128,2", T: "3"}, {S: "128,8"}, {S: "256,4", T: "3"}, {S: "256,2", T: "3"},
-         {S: "0", G: "3"}, {S: "0", G: "4"}, {S: "0", "NVLLM_GEMM_2CTA": "2"}, {S: "0", "NVLLM_GEMM_BN": "128"}]
+KNOBS = [{}, {S: "0"}, {S: "64,4"}, {S: "64,2"}, {S: "128,4"}, {S: "128,2"}, {S: "128,8"}, {S: "256,4"}, {S: "256,2"},
+         {S: "64,4", T: "6"}]
 ALL = ("NVLLM_GEMM_BN", "NVLLM_GEMM_MCAST", "NVLLM_GEMM_2CTA", S, T, G)
 
 
