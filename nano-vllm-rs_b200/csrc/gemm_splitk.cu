@@ -1,4 +1,4 @@
-// gemm_splitk.cu — K5'': split-K variant of the tcgen05 GEMM for the decode-sized projections (M <= 256 rows).
+// gemm_splitk.cu — K5'': split-K variant of the tcgen05 GEMM for the decode-sized projections (M <= 512 rows).
 //
 // Why: measured in-graph (profiles/r01_gemm_ingraph_v1.jsonl) the small-M GEMMs cost ~0.31 us per 64-wide k-block per
 // CTA whatever the tile width — each SM can only ingest ~35-45 B/clk through TMA, and every CTA of a 128 x BN tile has
@@ -295,7 +295,7 @@ long splitk_cost(int bn, int sk, int k) {
 bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_bn, int* out_sk) {
   const char* e = getenv("NVLLM_GEMM_SPLITK");
   if (e && e[0] == '0' && e[1] == 0) return false;
-  if (m > 256 || k % 64 != 0) return false;
+  if (m > 512 || k % 64 != 0) return false;  // up to four 128-row tile rows (the TP decode batches of 512 sequences)
   const int sms = sm_count();
   const int mt = (m + 127) / 128, num_kb = k / 64;
   auto legal = [&](int bn, int sk) {

@@ -414,8 +414,11 @@ static bool want_2cta(int m, int n, int k) {
 }
 
 static bool use_mcast() {
-  const char* e = getenv("NVLLM_GEMM_MCAST");  // A/B knob: 0 disables the x-multicast clusters
-  return !(e && e[0] == '0');
+  // x-multicast clusters: OFF by default.  In-graph they measured 5-7 % SLOWER than plain tiles on every shape they
+  // apply to (the bytes still have to enter every SM; the bound is the SM's TMA ingest, not L2 reads) and the long-K
+  // narrow-N projections they were built for now go to the cluster split-K kernel.  NVLLM_GEMM_MCAST=1 enables them.
+  const char* e = getenv("NVLLM_GEMM_MCAST");
+  return e && e[0] == '1';
 }
 
 static bool use_2cta() {

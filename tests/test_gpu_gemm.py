@@ -151,7 +151,7 @@ def test_gemm_splitk_every_config_vs_device_check(cuda, cfg, monkeypatch):
     """Cluster split-K GEMM (gemm_splitk.cu), every (BN, SK) instantiation forced through NVLLM_GEMM_SPLITK (re-read per
     call): M tail rows, K split 2/4/8 ways, against the CUDA-core check kernel and the same GEMM without split-K."""
     from nano_vllm_rs_b200 import ops
-    m, n, k = 200, 1024, 2048
+    m, n, k = (200, 1024, 2048) if cfg != "256,2" else (500, 2048, 2048)   # one case with four 128-row tile rows
     g = torch.Generator(device="cuda").manual_seed(11)
     x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
     w = (torch.randn((n, k), generator=g, device=cuda) * 0.05).to(torch.bfloat16)
@@ -187,7 +187,8 @@ def test_gemm_splitk_silu_every_config_vs_oracle(cuda, cfg, monkeypatch):
     assert (y != base).float().mean().item() < 0.05
 
 
-@pytest.mark.parametrize("m,n,k", [(256, 1024, 3072), (256, 1024, 2048), (4, 1024, 3072), (64, 2048, 4096), (1, 1024, 2048)])
+@pytest.mark.parametrize("m,n,k", [(256, 1024, 3072), (256, 1024, 2048), (4, 1024, 3072), (64, 2048, 4096), (1, 1024, 2048),
+                                   (512, 768, 4096), (512, 4096, 6144), (300, 4096, 2048)])
 def test_gemm_splitk_auto_decode_shapes(cuda, m, n, k):
     """The shapes the cost model sends to split-K by default (Qwen3-0.6B o_proj / down_proj at decode) vs the check kernel."""
     from nano_vllm_rs_b200 import ops
@@ -198,3 +199,18 @@ def test_gemm_splitk_auto_decode_shapes(cuda, m, n, k):
     r = ops.gemm_bf16(x, w, out_dtype=torch.float32, simt=True)
     torch.cuda.synchronize()
     assert_close(to_np_f32(y), to_np_f32(r), ATOL, RTOL, f"auto split-K {m}x{n}x{k}")
+
+
+@pytest.mark.parametrize("m,n,k", [(512, 768, 4096), (256, 1024, 3072), (130, 256, 2048)])
+def test_gemm_x_multicast_clusters_opt_in(cuda, m, n, k, monkeypatch):
+    """The x-multicast cluster mode (off by default since the in-graph measurements) still computes the same GEMM."""
+    from nano_vllm_rs_b200 import ops
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", "0")
+    monkeypatch.setenv("NVLLM_GEMM_MCAST", "1")
+    g = torch.Generator(device="cuda").manual_seed(m + n + k)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn((n, k), generator=g, device=cuda) * 0.02).to(torch.bfloat16)
+    y = ops.gemm_bf16(x, w)
+    r = ops.gemm_bf16(x, w, out_dtype=torch.float32, simt=True)
+    torch.cuda.synchronize()
+    assert_close(to_np_f32(y), to_np_f32(r), ATOL, RTOL, f"mcast gemm {m}x{n}x{k}")

@@ -20,8 +20,8 @@ SHAPES = {  # name: (M, N, K, kind)
     "8B/tp8 down": (512, 4096, 1536, "gemm"),
 }
 S, T, G = "NVLLM_GEMM_SPLITK", "NVLLM_GEMM_SK_STAGES", "NVLLM_GEMM_STAGES"
-KNOBS = [{}, {S: "0"}, {S: "64,4"}, {S: "64,2"}, {S: "128,4"}, {S: "128,2"}, {S: "128,8"}, {S: "256,4"}, {S: "256,2"},
-         {S: "64,4", T: "6"}]
+KNOBS = [{}, {S: "0"}, {S: "64,4"}, {S: "64,2"}, {S: "128,4"}, {S: "128,2"}, {S: "256,4"}, {S: "256,2"},
+         {S: "0", "NVLLM_GEMM_MCAST": "1"}, {S: "0", "NVLLM_GEMM_2CTA": "2"}]
 ALL = ("NVLLM_GEMM_BN", "NVLLM_GEMM_MCAST", "NVLLM_GEMM_2CTA", S, T, G)
 
 
