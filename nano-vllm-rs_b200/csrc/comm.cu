@@ -317,8 +317,19 @@ int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* resi
 
 int nvllm_comm_destroy(nvllm_comm* comm) {
   if (!comm) return 0;
+  cudaDeviceSynchronize();  // no kernel of this rank may still be reading peer memory
   for (int r = 0; r < comm->world; ++r)
     if (r != comm->rank && comm->sym_peer[r]) cudaIpcCloseMemHandle(comm->sym_peer[r]);
+  // Freeing exported memory while another process still has it mapped is undefined behaviour (observed as a hang at
+  // process teardown): rendezvous once more — every rank has closed its peer mappings before anyone frees its region.
+  if (comm->sym_local && comm->comm && nvllm::nccl().ok && comm->world > 1) {
+    cudaStream_t st = nullptr;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess) {
+      nvllm::nccl().AllReduce(comm->sym_local, comm->sym_local, 1, nvllm::ncclFloat32, nvllm::ncclSum, comm->comm, st);
+      cudaStreamSynchronize(st);
+      cudaStreamDestroy(st);
+    }
+  }
   if (comm->sym_local) cudaFree(comm->sym_local);
   if (comm->comm && nvllm::nccl().ok) nvllm::nccl().CommDestroy(comm->comm);
   delete comm;

@@ -48,12 +48,17 @@ def _tp_worker(rank, world, port, arch, prompts, max_tokens, q):
             sched.postprocess(toks)
         say(f"{len(trace)} steps done")
         q.put((rank, "ok", trace))
+        q.close(); q.join_thread()        # results are with the parent before any teardown starts
         dist.barrier()
+        del runner, sched
         _ffi.check(lib.nvllm_comm_destroy(h))
-        dist.destroy_process_group()
+        say("communicator destroyed")
+        os._exit(0)                       # skip interpreter / NCCL static teardown: nothing left to check
     except Exception:  # noqa: BLE001
         import traceback
         q.put((rank, "fail: " + traceback.format_exc(), None))
+        q.close(); q.join_thread()
+        os._exit(1)
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -75,12 +80,17 @@ def test_tp_engine_matches_single_gpu(cuda, world):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29600 + os.getpid() % 2000
-    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, arch, prompts, max_tokens, q)) for r in range(world)]
+    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, arch, prompts, max_tokens, q), daemon=True)
+             for r in range(world)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=300) for _ in procs], key=lambda r: r[0])
-    for p in procs:
-        p.join(timeout=60)
+    for p in procs:           # teardown of a rank must never hold the test (or pytest's exit) hostage
+        p.join(timeout=20)
+        if p.is_alive():
+            print(f"[tp test] rank process {p.pid} still alive 20 s after reporting: killing it", flush=True)
+            p.kill()
+            p.join(timeout=5)
     for rank, status, _ in res:
         assert status == "ok", f"rank {rank}: {status}"
     traces = [r[2] for r in res]
