@@ -168,6 +168,11 @@ def workload(args):
     return model, wl, prompt, K, W
 
 
+def workload_name(model, wl):
+    return (f"{model} bf16 decode: {wl['seqs']} concurrent seqs, paged KV block 256, "
+            f"{wl['prompt']}-token prompts + {wl['decode']} decode steps")
+
+
 def reference_arm(args):
     """bench.py --impl reference: the reference's own CPU implementation of the path.  The Rust crate cannot be built
     here (no toolchain, invalid manifest, type errors on the path — DESIGN.md), so this times the oracle port."""
@@ -182,7 +187,9 @@ def reference_arm(args):
     line = {"impl": "reference", "metric": "decode_tokens_per_s", "value": round(tps, 2), "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": K_cpu, "warmup": W_cpu, "ms_per_step": round(ms, 2), "higher_is_better": True,
             "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{model} decode step, CPU oracle port of the reference algorithm", "sample": desc},
+            "config": {"workload": workload_name(model, wl) + " — CPU oracle port of the reference algorithm (f32) on a "
+                                   "bounded sample of the workload's sequences", "sample": desc,
+                       "parallelism": "host cores (the reference has no GPU or multi-GPU path that runs)"},
             "cpu_baseline": {"value": round(tps, 2), "unit": "tokens/s", "cores": cores, "kind": "port", "sample": desc},
             "e2e": {"value": round(tps, 2), "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -295,8 +302,7 @@ def main():
         "metric": "decode_tokens_per_s", "value": round(B * K / (dev_ms * 1e-3), 1), "unit": "tokens/s", "n_gpus": world,
         "steps": K, "warmup": max(W, 3), "ms_per_step": round(dev_ms / K, 4), "higher_is_better": True,
         "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"{model} bf16 decode: {B} concurrent seqs, paged KV block 256, "
-                               f"{wl['prompt']}-token prompts + {wl['decode']} decode steps; timed steps at context "
+        "config": {"workload": workload_name(model, wl) + f"; timed steps at context "
                                f"{ctx_first}..{ctx_last} (workload mean {wl['prompt'] + wl['decode'] // 2})",
                    "seqs": B, "prompt_len_used": prompt, "parallelism": f"tp{world}",
                    "cuda_graphs": not args.eager, "l2_note": "inputs larger than L2: one step reads "
