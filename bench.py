@@ -288,13 +288,15 @@ def main():
     peak, peak_src = peaks()
     achieved = att_bytes / (att_ms * 1e-3) / 1e9
     layers = cfg.num_hidden_layers
-    traffic = None
+    traffic, traffic_capture = None, None
     prof = os.path.join(ROOT, "profiles", "decode_attention_ncu.json")  # dram bytes/launch from the committed ncu capture
     if os.path.exists(prof):
         try:
             pj = json.load(open(prof))
             if pj.get("model") == model and pj.get("batch") == B:
                 traffic = pj.get("dram_bytes_per_launch")
+                # the capture ran at its own context length: its algorithmic bytes are the ones to compare traffic with
+                traffic_capture = {k: pj.get(k) for k in ("context", "alg_bytes_per_launch", "ratio")}
         except Exception:
             pass
     cap = cfg.max_model_len // 256
@@ -315,7 +317,8 @@ def main():
         "launches_per_step": int(launches),
         "roofline": {"kernel": "paged_decode_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                      "unit": "GB/s", "frac": round(achieved / peak, 4), "frac_of_8TBps_nominal": round(achieved / 8000.0, 4),
-                     "peak_source": peak_src, "traffic": traffic, "alg_bytes_per_launch": int(att_bytes),
+                     "peak_source": peak_src, "traffic": traffic, "traffic_capture": traffic_capture,
+                     "alg_bytes_per_launch": int(att_bytes),
                      "ms_per_launch": round(att_ms, 5),
                      "share_of_step": round(att_ms * layers / (dev_ms / K), 4),
                      "how": "CUDA events on the runner's stream around re-launches of the kernel on the live batch, "
