@@ -3,11 +3,11 @@
 // The reference samples one row at a time on the host: a blocking scalar read per parameter, two full sorts of the
 // vocabulary (top-k, top-p), a softmax and an unseeded Tensor::rand.  Here one CTA owns one row of the f32 logits and
 // never sorts: both filters are *selections*, done MSB-first over the order-preserving integer image of the scaled
-// logits with 256-bin shared-memory histograms (4 passes each over a row that stays in L2):
+// logits with shared-memory histograms (3 passes each over 8 + 12 + 12 key bits, 16-byte loads, warp-aggregated updates):
 //   top-k  (sampler.rs:115-149)  k-th largest key by COUNT; ties at the threshold keep the lowest indices (the
 //                                reference's stable sort), resolved by an ordered ballot scan only when they straddle k
 //   top-p  (sampler.rs:152-191)  smallest prefix of the descending order whose probability mass reaches p, found by
-//                                MASS: exp(s - max) in 32.32 fixed point, so every sum is an integer sum (order-free,
+//                                MASS: exp(s - max) in 0.32 fixed point, so every sum is an integer sum (order-free,
 //                                deterministic); target = ceil(p * total)
 //   Gumbel-max (sampler.rs:194-219) argmax(s + g), g = -log(-log(u)), first maximum wins
 // Rows with temperature == 0 take the same final pass without filters or noise (greedy, sampler.rs:79-81,109-112).
@@ -20,8 +20,9 @@
 namespace nvllm {
 namespace {
 
-constexpr int kThreads = 512;
+constexpr int kThreads = 1024;
 constexpr int kWarps = kThreads / 32;
+constexpr int kBins = 4096;  // three selection passes over 8 + 12 + 12 key bits (see radix_select)
 constexpr uint64_t kGolden = 0x9E3779B97F4A7C15ull;
 constexpr unsigned kFull = 0xffffffffu;
 
@@ -40,9 +41,11 @@ __device__ __forceinline__ float okey_inv(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
 }
 __device__ __forceinline__ float scaled(float x, float T) { return T == 1.0f ? x : __fdiv_rn(x, T); }  // sampler.rs:84-88
-// exp(s - m) in 32.32 fixed point (s <= m, so the value is in [0, 2^32])
-__device__ __forceinline__ unsigned long long fx_exp(float s, float m) {
-  return __float2ull_rz(expf(s - m) * 4294967296.0f);
+// exp(s - m) in 0.32 fixed point (s <= m): [0, 2^32 - 1] — the maximum itself is capped one unit below 2^32 so that a
+// weight fits 32 bits (two 16-bit warp reductions per histogram update)
+__device__ __forceinline__ uint32_t fx_exp(float s, float m) {
+  const unsigned long long w = __float2ull_rz(expf(s - m) * 4294967296.0f);
+  return w > 0xffffffffull ? 0xffffffffu : static_cast<uint32_t>(w);
 }
 
 // keep(key, i) <=> key > sel.key || (key == sel.key && i <= sel.cut)
@@ -54,7 +57,7 @@ __device__ __forceinline__ bool keeps(const Sel& s, uint32_t key, uint32_t i) {
 }
 
 struct Shared {
-  unsigned long long hist[256];
+  unsigned long long hist[kBins];
   unsigned long long need, eq;
   float redf[32];
   int redi[32];
@@ -63,32 +66,91 @@ struct Shared {
   uint32_t cut;
 };
 
-// MSB-first radix selection over the keys of one row, largest first.  weight(key, i) is the element's contribution
-// (0 = not a candidate).  Finds the key K with  sum{w : key > K} < target <= sum{w : key >= K}  and returns how much of
-// the target the group key == K has to supply (`need`, >= 1) and that group's total weight (`eq`).
-// MASS == true: the target is ceil(p * total weight), fixed after the first pass.
+// Visits the row with 16-byte loads (two in flight per thread).  f(v, i0, n): v[0..n) are elements i0 .. i0+n-1; f is
+// called the SAME number of times by every thread of the CTA (n == 0 for idle slots), so it may use full-warp intrinsics.
+template <typename F>
+__device__ __forceinline__ void for_each4(const float* __restrict__ row, int V, F f) {
+  const int tid = threadIdx.x;
+  if ((reinterpret_cast<uintptr_t>(row) & 15u) == 0) {
+    const int nvec = V >> 2;
+    const float4* r4 = reinterpret_cast<const float4*>(row);
+    for (int base = 0; base < nvec; base += 2 * kThreads) {
+      const int j0 = base + tid, j1 = j0 + kThreads;
+      float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
+      if (j0 < nvec) q0 = __ldg(r4 + j0);
+      if (j1 < nvec) q1 = __ldg(r4 + j1);
+      const float v0[4] = {q0.x, q0.y, q0.z, q0.w}, v1[4] = {q1.x, q1.y, q1.z, q1.w};
+      f(v0, 4 * j0, j0 < nvec ? 4 : 0);
+      if (base + kThreads < nvec) f(v1, 4 * j1, j1 < nvec ? 4 : 0);  // block-uniform condition
+    }
+    const int t0 = nvec << 2;
+    if (t0 < V) {  // V % 4 trailing elements: thread 0 takes them, everybody makes the call
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      int n = 0;
+      if (tid == 0) { n = V - t0; for (int e = 0; e < n; ++e) v[e] = row[t0 + e]; }
+      f(v, t0, n);
+    }
+  } else {
+    for (int base = 0; base < V; base += kThreads) {
+      const int i = base + tid;
+      float v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (i < V) v[0] = row[i];
+      f(v, i, i < V ? 1 : 0);
+    }
+  }
+}
+
+// MSB-first radix selection over the keys of one row, largest first, 8 + 12 + 12 bits.  weight(key, i) is the element's
+// contribution (0 = not a candidate).  Finds the key K with  sum{w : key > K} < target <= sum{w : key >= K}  and returns
+// how much of the target the group key == K has to supply (`need`, >= 1) and that group's total weight (`eq`).
+// MASS == true: weights are 32-bit masses and the target is ceil(p * total), fixed after the first pass; MASS == false:
+// weights are 0/1.  Histogram updates are aggregated per warp (match_any on the bin: logits cluster in a handful of
+// exponent bins, un-aggregated shared-memory atomics serialise on them).  row_max (optional) receives max(scaled row).
 template <bool MASS, typename WF>
 __device__ void radix_select(Shared& sh, const float* __restrict__ row, int V, float T, WF weight, unsigned long long target,
-                             double p, uint32_t& out_key, unsigned long long& out_need, unsigned long long& out_eq) {
+                             double p, uint32_t& out_key, unsigned long long& out_need, unsigned long long& out_eq,
+                             float* row_max) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   uint32_t prefix = 0, mask = 0;
   unsigned long long rem = target;
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 24 - 8 * pass;
-    for (int b = tid; b < 256; b += kThreads) sh.hist[b] = 0ull;
+  float mx = -INFINITY;
+#pragma unroll 1
+  for (int pass = 0; pass < 3; ++pass) {
+    // First digit = sign + 7 exponent bits only: every element takes part in the first pass, and the warp-aggregated
+    // update costs ~ the number of DISTINCT bins in a warp (a handful at this width); later passes see few candidates.
+    const int shift = pass == 0 ? 24 : (pass == 1 ? 12 : 0);
+    const int nbins = pass == 0 ? 256 : 4096;
+    for (int b = tid; b < nbins; b += kThreads) sh.hist[b] = 0ull;
     __syncthreads();
-    for (int i = tid; i < V; i += kThreads) {
-      const uint32_t key = okey(scaled(row[i], T));
-      if ((key & mask) == prefix) {
-        const unsigned long long w = weight(key, static_cast<uint32_t>(i));
-        if (w) atomicAdd(&sh.hist[(key >> shift) & 255u], w);
-      }
-    }
-    __syncthreads();
-    if (warp == 0) {  // lane l owns bins 255-8l .. 248-8l, scanned from the top
-      unsigned long long loc[8], s = 0ull;
+    for_each4(row, V, [&](const float (&v)[4], int i0, int n) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { loc[j] = sh.hist[255 - 8 * lane - j]; s += loc[j]; }
+      for (int e = 0; e < 4; ++e) {
+        bool part = e < n;
+        const float s = scaled(v[e], T);
+        const uint32_t key = okey(s);
+        if (pass == 0 && row_max != nullptr && part) mx = fmaxf(mx, s);
+        part = part && (key & mask) == prefix;
+        const uint32_t w = part ? static_cast<uint32_t>(weight(key, static_cast<uint32_t>(i0 + e))) : 0u;
+        part = part && w != 0u;
+        if (__any_sync(kFull, part)) {
+          const uint32_t bin = part ? ((key >> shift) & static_cast<uint32_t>(nbins - 1)) : 0xffffffffu;
+          const unsigned peers = __match_any_sync(kFull, bin);
+          unsigned long long sum;
+          if (MASS) {
+            const uint32_t lo = __reduce_add_sync(peers, w & 0xffffu), hi = __reduce_add_sync(peers, w >> 16);
+            sum = (static_cast<unsigned long long>(hi) << 16) + lo;
+          } else {
+            sum = static_cast<unsigned long long>(__popc(peers));
+          }
+          if (part && lane == __ffs(peers) - 1) atomicAdd(&sh.hist[bin], sum);
+        }
+      }
+    });
+    __syncthreads();
+    if (warp == 0) {  // lane l owns bins nbins-1-per*l .. nbins-per*(l+1), scanned from the top
+      const int per = nbins / 32, top = nbins - 1 - per * lane;
+      unsigned long long s = 0ull;
+      for (int j = 0; j < per; ++j) s += sh.hist[top - j];
       unsigned long long incl = s;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -106,26 +168,23 @@ __device__ void radix_select(Shared& sh, const float* __restrict__ row, int V, f
       const unsigned long long excl = incl - s;
       if (excl < rem && rem <= incl) {  // exactly one lane
         unsigned long long c = excl;
-        int bsel = -1;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (bsel < 0) {
-            if (c + loc[j] >= rem) { bsel = 255 - 8 * lane - j; sh.need = rem - c; sh.eq = loc[j]; }
-            else c += loc[j];
-          }
+        for (int j = 0; j < per; ++j) {
+          const unsigned long long h = sh.hist[top - j];
+          if (c + h >= rem) { sh.sel_bin = top - j; sh.need = rem - c; sh.eq = h; break; }
+          c += h;
         }
-        sh.sel_bin = bsel;
       }
     }
     __syncthreads();
     prefix |= static_cast<uint32_t>(sh.sel_bin) << shift;
-    mask |= 255u << shift;
+    mask |= static_cast<uint32_t>(nbins - 1) << shift;
     rem = sh.need;
     out_eq = sh.eq;
     __syncthreads();
   }
   out_key = prefix;
   out_need = rem;
+  if (row_max != nullptr) *row_max = mx;  // per-thread partial; the caller reduces it
 }
 
 // Smallest index I with #{i <= I : pred(i)} == need (pred true for at least `need` elements).  Each warp counts a
@@ -197,28 +256,36 @@ sample_kernel(int64_t* __restrict__ out_ids, const float* __restrict__ logits, i
   Sel sk{0u, 0xffffffffu}, sp{0u, 0xffffffffu};  // key >= 0 always holds: no filtering
 
   if (!greedy) {
-    // ---- top-k: the k-th largest key by count (sampler.rs:115-149) ----
     const int k = top_k != nullptr ? top_k[b] : 0;
-    if (k > 0 && k < V) {
+    const float p = top_p != nullptr ? top_p[b] : 0.0f;
+    const bool do_k = k > 0 && k < V, do_p = p > 0.0f && p < 1.0f;
+    float m = -INFINITY;  // max of the scaled row (it always survives top-k), needed by top-p only
+    bool have_m = false;
+    // ---- top-k: the k-th largest key by count (sampler.rs:115-149) ----
+    if (do_k) {
       uint32_t key;
       unsigned long long need, eq;
-      radix_select<false>(sh, row, V, T, [](uint32_t, uint32_t) { return 1ull; }, static_cast<unsigned long long>(k), 0.0, key,
-                          need, eq);
+      radix_select<false>(sh, row, V, T, [](uint32_t, uint32_t) { return 1u; }, static_cast<unsigned long long>(k), 0.0, key,
+                          need, eq, do_p ? &m : nullptr);
+      have_m = do_p;
       sk.key = key;
       if (need < eq)  // ties straddle k: the stable sort keeps the lowest indices
         sk.cut = ordered_cut(sh, V, [&](uint32_t i) { return okey(scaled(row[i], T)) == key; }, static_cast<uint32_t>(need));
     }
     // ---- top-p: smallest descending prefix whose softmax mass reaches p (sampler.rs:152-191) ----
-    const float p = top_p != nullptr ? top_p[b] : 0.0f;
-    if (p > 0.0f && p < 1.0f) {
-      float m = -INFINITY;  // the maximum always survives top-k
-      for (int i = tid; i < V; i += kThreads) m = fmaxf(m, scaled(row[i], T));
+    if (do_p) {
+      if (!have_m)
+        for_each4(row, V, [&](const float (&v)[4], int, int n) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (e < n) m = fmaxf(m, scaled(v[e], T));
+        });
       m = block_max(sh, m);
       const Sel skc = sk;
-      auto w_of = [&](uint32_t key, uint32_t i) { return keeps(skc, key, i) ? fx_exp(okey_inv(key), m) : 0ull; };
+      auto w_of = [&](uint32_t key, uint32_t i) { return keeps(skc, key, i) ? fx_exp(okey_inv(key), m) : 0u; };
       uint32_t key;
       unsigned long long need, eq;
-      radix_select<true>(sh, row, V, T, w_of, 0ull, static_cast<double>(p), key, need, eq);
+      radix_select<true>(sh, row, V, T, w_of, 0ull, static_cast<double>(p), key, need, eq, nullptr);
       sp.key = key;
       const unsigned long long w1 = fx_exp(okey_inv(key), m);  // every element of the tie group weighs the same
       if (w1 > 0ull) {
@@ -234,25 +301,33 @@ sample_kernel(int64_t* __restrict__ out_ids, const float* __restrict__ logits, i
   const uint64_t seed = greedy ? 0ull : row_seeds[b];
   float best = -INFINITY;
   int bidx = 0x7fffffff, kept = 0;
-  for (int i = tid; i < V; i += kThreads) {
-    const float x = row[i];
-    float score;
-    bool keep = true;
-    if (greedy) {
-      score = x;
-    } else {
-      const float s = scaled(x, T);
-      const uint32_t key = okey(s);
-      keep = keeps(sk, key, static_cast<uint32_t>(i)) && keeps(sp, key, static_cast<uint32_t>(i));
-      const uint64_t h = mix64(seed + static_cast<uint64_t>(i + 1) * kGolden);
-      const float u = (static_cast<float>(h >> 41) + 0.5f) * 1.1920928955078125e-07f;  // 2^-23; in (0, 1)
-      const float uc = fminf(fmaxf(u, 1e-8f), 1.0f - 1e-8f);                             // sampler.rs:211-212
-      score = keep ? s + (-logf(-logf(uc))) : -INFINITY;
+  for_each4(row, V, [&](const float (&v)[4], int i0, int n) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (e < n) {
+        const int i = i0 + e;
+        float score;
+        bool keep = true;
+        if (greedy) {
+          score = v[e];
+        } else {
+          const float s = scaled(v[e], T);
+          const uint32_t key = okey(s);
+          keep = keeps(sk, key, static_cast<uint32_t>(i)) && keeps(sp, key, static_cast<uint32_t>(i));
+          score = -INFINITY;
+          if (keep) {  // the noise is only needed for survivors
+            const uint64_t h = mix64(seed + static_cast<uint64_t>(i + 1) * kGolden);
+            const float u = (static_cast<float>(h >> 41) + 0.5f) * 1.1920928955078125e-07f;  // 2^-23; in (0, 1)
+            const float uc = fminf(fmaxf(u, 1e-8f), 1.0f - 1e-8f);                             // sampler.rs:211-212
+            score = s + (-logf(-logf(uc)));
+          }
+        }
+        if (kept_mask != nullptr) kept_mask[static_cast<int64_t>(b) * V + i] = keep ? 1 : 0;
+        kept += keep ? 1 : 0;
+        if (score > best || (score == best && i < bidx)) { best = score; bidx = i; }
+      }
     }
-    if (kept_mask != nullptr) kept_mask[static_cast<int64_t>(b) * V + i] = keep ? 1 : 0;
-    kept += keep ? 1 : 0;
-    if (score > best || (score == best && i < bidx)) { best = score; bidx = i; }
-  }
+  });
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(kFull, best, o);
