@@ -46,6 +46,10 @@ struct PrefillParams {
   float scale_log2;
 };
 
+// POLY: how many of every 4 exponentials go to the FMA-pipe polynomial instead of MUFU.EX2 (1 = the validated default;
+// the ncu capture of round 1 shows the XU pipe saturated and the tensor pipe at 25 %, so 2 and 3 are kept as variants,
+// NVLLM_PREFILL_POLY).
+template <int POLY>
 __global__ void __launch_bounds__(pf::kThreads, 1)
 prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const PrefillParams p) {
@@ -257,8 +261,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const int c = h2 * 64 + e * 2;
           const float a0 = fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff);
           const float a1 = fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff);
-          const float p0 = fast_exp2(a0);                               // MUFU
-          const float p1 = (e & 1) ? exp2_poly(a1) : fast_exp2(a1);     // every 4th element on the FMA pipe
+          const float p0 = (POLY >= 3 && (e & 1)) ? exp2_poly(a0) : fast_exp2(a0);               // MUFU (POLY 3: half of them FMA)
+          const float p1 = (POLY >= 2 || (POLY == 1 && (e & 1))) ? exp2_poly(a1) : fast_exp2(a1);  // FMA-pipe share per POLY
           ls4[e & 3] += p0 + p1;
           pk[e] = pack_bf16x2(p0, p1);      // low half = even key: consecutive K elements share a 32-bit column
         }
@@ -369,12 +373,18 @@ extern "C" int nvllm_varlen_prefill_attention(void* out, const void* q, const vo
   p.scale_log2 = scale * 1.4426950408889634f;
   static bool attr_set = false;
   if (!attr_set) {
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
     attr_set = true;
   }
   (void)max_seqlen_k;
   dim3 grid((max_seqlen_q + 2 * pf::BM - 1) / (2 * pf::BM), num_heads, batch);
-  NVLLM_CUDA(launch_pdl(prefill_attn_kernel, grid, dim3(pf::kThreads), pf::kSmemBytes, static_cast<cudaStream_t>(stream),
-                        tq, tk, tv, p));
+  const char* pe = getenv("NVLLM_PREFILL_POLY");
+  const int poly = pe ? atoi(pe) : 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (poly == 2) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<2>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
+  else if (poly == 3) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<3>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
+  else NVLLM_CUDA(launch_pdl(prefill_attn_kernel<1>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
   return 0;
 }
