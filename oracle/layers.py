@@ -243,7 +243,7 @@ def mix64(x):
 def sampler_row_seed(engine_seed, seq_id, num_tokens):
     with np.errstate(over="ignore"):
         inner = mix64(np.uint64(seq_id) * GOLDEN + np.uint64(num_tokens))
-        return int(mix64(np.uint64(engine_seed) ^ inner))
+        return int(mix64(np.uint64(int(engine_seed) & 0xFFFFFFFFFFFFFFFF) ^ inner))  # i32 seed sign-extended to u64
 
 
 def sampler_uniform(row_seed, n):
