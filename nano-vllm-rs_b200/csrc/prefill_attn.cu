@@ -10,7 +10,7 @@
 //                       32 KiB slots; dense K/V via a 2-D map, paged K/V via a 4-D map (d, token, head, block) + block_tables
 //   warp 9 (one lane)   MMA issuer for both groups: S = Q . K^T (8 x tcgen05.mma M128 N128 K16, both operands K-major in
 //                       shared memory) and O += P . V (8 x tcgen05.mma with A = P read from TENSOR MEMORY, V MN-major)
-//   RG threads          tcgen05.ld S row -> row max -> exp2 (3/4 on MUFU, 1/4 by a polynomial on the FMA pipe) ->
+//   RG threads          tcgen05.ld S row -> row max -> exp2 (3/4 on MUFU, 1/4 by an XU-free polynomial on the FMA pipe) ->
 //                       P as packed bf16 written BACK INTO TMEM over the S columns (tcgen05.st; each thread only touches its
 //                       own lane, so no cross-thread hazard) -> mbarrier arrive.  No shared-memory round trip for P.
 //                       O accumulates in TMEM across tiles; the reference maximum is refreshed lazily (only when a tile
@@ -46,9 +46,9 @@ struct PrefillParams {
   float scale_log2;
 };
 
-// POLY: how many of every 4 exponentials go to the FMA-pipe polynomial instead of MUFU.EX2 (1 = the validated default;
-// the ncu capture of round 1 shows the XU pipe saturated and the tensor pipe at 25 %, so 2 and 3 are kept as variants,
-// NVLLM_PREFILL_POLY).
+// POLY: how many of every 4 exponentials go to a polynomial instead of MUFU.EX2 (NVLLM_PREFILL_POLY): 1 / 2 / 3 with the
+// floor-based polynomial (the first version; its FRND / F2I also run on the XU pipe, so 2 and 3 gain nothing over 1),
+// 4 / 5 / 6 = 1/4, 1/2, 3/4 with the XU-free polynomial.  Default 4 (measured best: profiles/r01_prefill_microbench_v5_polysplit.jsonl).
 template <int POLY>
 __global__ void __launch_bounds__(pf::kThreads, 1)
 prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
@@ -211,6 +211,19 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
       return __int_as_float(__float_as_int(pfr) + (static_cast<int>(n) << 23));
     };
 
+    // The same without any XU-pipe instruction (the ncu source page of round 1 shows FRND.FLOOR and F2I.FLOOR of the
+    // version above on the XU pipe next to MUFU.EX2 — it relieves nothing): round-to-nearest by the 1.5 * 2^23 magic add,
+    // f in [-0.5, 0.5], degree-3 minimax polynomial (rel. err 7.5e-5), n taken from the low mantissa bits of the sum.
+    auto exp2_poly2 = [](float x) {
+      x = fmaxf(x, -126.f);
+      const float t = x + 12582912.f;
+      const float f = x - (t - 12582912.f);
+      float pfr = fmaf(f, 0.05517210811376572f, 0.24261118471622467f);
+      pfr = fmaf(pfr, f, 0.693260908126831f);
+      pfr = fmaf(pfr, f, 0.9999280571937561f);
+      return __int_as_float(__float_as_int(pfr) + (__float_as_int(t) << 23));
+    };
+
     float m_ref = -INFINITY, l_run = 0.f;  // m_ref: the (stale-by-design) maximum the exponentials are taken against
     for (int j = 0; j < n_my; ++j) {
       mbar_wait(s_full(g), j & 1);
@@ -261,8 +274,14 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
           const int c = h2 * 64 + e * 2;
           const float a0 = fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff);
           const float a1 = fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff);
-          const float p0 = (POLY >= 3 && (e & 1)) ? exp2_poly(a0) : fast_exp2(a0);               // MUFU (POLY 3: half of them FMA)
-          const float p1 = (POLY >= 2 || (POLY == 1 && (e & 1))) ? exp2_poly(a1) : fast_exp2(a1);  // FMA-pipe share per POLY
+          float p0, p1;
+          if constexpr (POLY <= 3) {
+            p0 = (POLY >= 3 && (e & 1)) ? exp2_poly(a0) : fast_exp2(a0);               // MUFU (POLY 3: half of them FMA)
+            p1 = (POLY >= 2 || (POLY == 1 && (e & 1))) ? exp2_poly(a1) : fast_exp2(a1);  // FMA-pipe share per POLY
+          } else {  // POLY 4 / 5 / 6: 1/4, 1/2, 3/4 of the exponentials on the XU-free polynomial
+            p0 = (POLY >= 6 && (e & 1)) ? exp2_poly2(a0) : fast_exp2(a0);
+            p1 = (POLY >= 5 || (e & 1)) ? exp2_poly2(a1) : fast_exp2(a1);
+          }
           ls4[e & 3] += p0 + p1;
           pk[e] = pack_bf16x2(p0, p1);      // low half = even key: consecutive K elements share a 32-bit column
         }
@@ -376,15 +395,21 @@ extern "C" int nvllm_varlen_prefill_attention(void* out, const void* q, const vo
     NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
     NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
     NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
+    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
     attr_set = true;
   }
   (void)max_seqlen_k;
   dim3 grid((max_seqlen_q + 2 * pf::BM - 1) / (2 * pf::BM), num_heads, batch);
   const char* pe = getenv("NVLLM_PREFILL_POLY");
-  const int poly = pe ? atoi(pe) : 1;
+  const int poly = pe ? atoi(pe) : 4;  // XU-free polynomial on 1/4 of the exponentials: +26 % at 4K, 1060 TFLOP/s at 32K
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (poly == 2) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<2>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
   else if (poly == 3) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<3>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
+  else if (poly == 4) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<4>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
+  else if (poly == 5) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<5>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
+  else if (poly == 6) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<6>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
   else NVLLM_CUDA(launch_pdl(prefill_attn_kernel<1>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
   return 0;
 }
