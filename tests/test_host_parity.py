@@ -140,3 +140,85 @@ def test_config_defaults_and_validate():
     with pytest.raises(Exception):
         E.Config("qwen3-8b", tensor_parallel_size=3).validate()     # qwen3.rs:111-113
     E.Config("qwen3-32b", tensor_parallel_size=8, tp_rank=7, max_model_len=32768 + 64).validate()
+
+
+def test_cfg2_full_size_trace_appendix_b():
+    """BASELINE configs[1] at FULL size through the C++ scheduler: 256 x 512-token prompts,
+    512 new tokens, block 256 — 4 prefill steps of 64 sequences, seq j owns blocks [2j, 2j+1], takes block 512+j at the
+    first decode step and 768+j at length 769; 1024 blocks in total; slot mapping / context lengths follow."""
+    rng = np.random.default_rng(1234)
+    B, L, NEW, bs = 256, 512, 512, 256
+    cfg = E.Config("qwen3-0.6b", kvcache_block_size=bs, num_kvcache_blocks=1024, max_num_batched_tokens=32768, max_num_seqs=256)
+    sc = E.Scheduler(cfg)
+    for _ in range(B):
+        sc.add_sequence(rng.integers(0, 151936, L), E.SamplingParams(temperature=0.0, max_tokens=NEW, ignore_eos=True))
+    for step in range(4):
+        b = sc.schedule()
+        assert b.is_prefill and len(b.seq_ids) == 64 and len(b.input_ids) == 32768 and b.block_tables is None
+        j0 = 64 * step
+        assert b.slot_mapping[0] == 2 * j0 * bs and b.slot_mapping[-1] == (2 * (j0 + 63) + 1) * bs + bs - 1
+        assert np.array_equal(b.cu_seqlens_q, np.arange(0, 32768 + 1, L, dtype=np.int32))
+        sc.postprocess(np.zeros(64, np.int64))
+    st = sc.get_stats()
+    assert st["waiting"] == 0 and st["running"] == B and st["used_blocks"] == 512 and st["cached_blocks"] == 512
+    for k in range(NEW - 1):                       # the prefill already produced completion #1
+        b = sc.schedule()
+        n = L + 1 + k                              # sequence length at this decode forward
+        assert not b.is_prefill and len(b.seq_ids) == B
+        assert (b.context_lens == n).all() and (b.positions == n - 1).all()
+        nblk = (n + bs - 1) // bs
+        assert b.block_tables.shape == (B, nblk)
+        j = np.arange(B)
+        assert np.array_equal(b.block_tables[:, 0], 2 * j) and np.array_equal(b.block_tables[:, 1], 2 * j + 1)
+        assert np.array_equal(b.block_tables[:, 2], 512 + j)
+        if nblk == 4:
+            assert np.array_equal(b.block_tables[:, 3], 768 + j)
+        last = b.block_tables[:, nblk - 1].astype(np.int64)
+        assert np.array_equal(b.slot_mapping.astype(np.int64), last * bs + (n - 1) % bs)
+        sc.postprocess(np.full(B, 7, np.int64))
+    st = sc.get_stats()
+    assert sc.is_finished() and st["finished"] == B and st["preemptions"] == 0 and st["used_blocks"] == 0
+    assert st["prefill_batches"] == 4 and st["decode_batches"] == NEW - 1
+
+
+def test_cfg4_full_size_shared_prefix_trace_appendix_b():
+    """BASELINE configs[3] at FULL size (Appendix B, cfg4): 256 sequences = one shared 4096-token prefix + 256 unique tokens;
+    17 full blocks each; sequence 0 allocates blocks 0..16, sequence k >= 1 hits blocks 0..15 (ref_count -> k + 1,
+    num_cached_tokens = 4096) and misses the 17th (chained hash differs) -> new block 16 + k; 7 sequences per prefill step
+    (admission counts the full 4352 tokens), 37 prefill steps, 272 blocks after prefill, + 256 at the first decode step."""
+    rng = np.random.default_rng(4321)
+    bs, B = 256, 256
+    prefix = rng.integers(0, 151936, 4096)
+    cfg = E.Config("qwen3-8b", kvcache_block_size=bs, num_kvcache_blocks=600, max_num_batched_tokens=32768, max_num_seqs=256,
+                   max_model_len=8192)
+    sc = E.Scheduler(cfg)
+    for _ in range(B):
+        sc.add_sequence(np.concatenate([prefix, rng.integers(0, 151936, 256)]),
+                        E.SamplingParams(temperature=0.0, max_tokens=2, ignore_eos=True))
+    steps, seen = 0, 0
+    while sc.get_stats()["waiting"] > 0:
+        b = sc.schedule()
+        assert b.is_prefill
+        n = len(b.seq_ids)
+        assert n == (7 if seen + 7 <= B else B - seen)
+        for i in range(n):
+            k = seen + i
+            q = b.cu_seqlens_q[i + 1] - b.cu_seqlens_q[i]
+            assert b.cu_seqlens_k[i + 1] - b.cu_seqlens_k[i] == 4352
+            assert q == (4352 if k == 0 else 256)            # only the uncached suffix is computed
+            if b.block_tables is not None:
+                want = list(range(16)) + [16 + k]
+                assert b.block_tables[i, :17].tolist() == want
+        seen += n
+        sc.postprocess(np.zeros(n, np.int64))
+        steps += 1
+    assert steps == 37
+    st = sc.get_stats()
+    assert st["used_blocks"] == 272 and st["cached_blocks"] == 272
+    assert sc.block_info(0)[0] == B and sc.block_info(15)[0] == B and sc.block_info(16)[0] == 1 and sc.block_info(17)[0] == 1
+    b = sc.schedule()                                        # first decode step: 4353 % 256 == 1 -> one new block each
+    assert not b.is_prefill and (b.context_lens == 4353).all()
+    assert np.array_equal(b.block_tables[:, 17], 272 + np.arange(B))
+    assert sc.get_stats()["used_blocks"] == 272 + 256
+    sc.postprocess(np.zeros(B, np.int64))
+    assert sc.is_finished() and sc.get_stats()["used_blocks"] == 0
