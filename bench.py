@@ -95,10 +95,11 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU oracle arm
-def cpu_decode_sample(model, ctx, sample_seqs, steps, warmup):
+def cpu_decode_sample(model, ctx, sample_seqs, steps, warmup, budget_s=None):
     """Times the CPU oracle (oracle/qwen3.py: numpy restatement of the reference algorithm — per-sequence block gather +
     dense softmax attention, f32) on `sample_seqs` sequences of the workload at context `ctx`; weights and KV are random
-    (timing only).  Returns (tokens/s, cores, description)."""
+    (timing only; drawn from one 16 Mi-element pool repeated cyclically, so that setting up 8B parameters takes seconds).
+    `budget_s` bounds the timed steps (at least one runs).  Returns (tokens/s, cores, description, ms/step)."""
     import numpy as np
     from oracle import host as H
     from oracle import qwen3 as Q
@@ -110,7 +111,8 @@ def cpu_decode_sample(model, ctx, sample_seqs, steps, warmup):
     shapes = Q.seeded_weights.__doc__  # noqa: F841 (ids documented there)
     H_, Hkv, D, hid, I, V = (cfg[k] for k in ("num_attention_heads", "num_key_value_heads", "head_dim", "hidden_size",
                                               "intermediate_size", "vocab_size"))
-    rnd = lambda *s: (rng.standard_normal(s, dtype=np.float32) * np.float32(0.02))
+    pool = rng.standard_normal(1 << 24, dtype=np.float32) * np.float32(0.02)
+    rnd = lambda *s: np.resize(pool, s)
     w["model.embed_tokens.weight"] = rnd(V, hid)
     w["model.norm.weight"] = np.ones(hid, np.float32)
     if not cfg["tie_word_embeddings"]:
@@ -126,8 +128,8 @@ def cpu_decode_sample(model, ctx, sample_seqs, steps, warmup):
             w[p + n + ".weight"] = rnd(*shp)
     m = Q.Qwen3Oracle(cfg, w, sample_seqs * nblk_seq, bs)
     for l in range(cfg["num_hidden_layers"]):
-        m.k_cache[l][:] = rng.standard_normal(m.k_cache[l].shape, dtype=np.float32)
-        m.v_cache[l][:] = rng.standard_normal(m.v_cache[l].shape, dtype=np.float32)
+        m.k_cache[l][:] = np.resize(pool, m.k_cache[l].shape) * np.float32(50.0)
+        m.v_cache[l][:] = np.resize(pool[::-1], m.v_cache[l].shape) * np.float32(50.0)
     seqs = []
     for i in range(sample_seqs):
         s = H.Sequence(rng.integers(0, V, ctx).tolist(), H.SamplingParams(temperature=0.0, max_tokens=1 << 30), bs)
@@ -146,6 +148,8 @@ def cpu_decode_sample(model, ctx, sample_seqs, steps, warmup):
             times.append(dt)
         for s, t in zip(seqs, toks):
             s.append_token(int(t))
+        if budget_s is not None and times and sum(times) + times[-1] > budget_s:
+            break
     cores = os.cpu_count() or 1
     tps = sample_seqs * len(times) / sum(times)
     desc = (f"{len(times)} decode step(s) of {sample_seqs} of the workload's sequences at context {ctx} "
@@ -181,9 +185,12 @@ def reference_arm(args):
         return
     model, wl, prompt, K, W = workload(args)
     ctx = prompt + W + K // 2
-    sample = 32 if K <= 8 else (16 if K <= 24 else 8)
-    K_cpu, W_cpu = max(1, min(K, 64)), max(1, min(W, 2))
-    tps, cores, desc, ms = cpu_decode_sample(model, ctx, sample, K_cpu, W_cpu)
+    # bounded sample: the whole arm ends within a few minutes whatever --steps says (about 60 s of timed steps)
+    big = model != "qwen3-0.6b"
+    sample = 8 if big else (32 if K <= 8 else 16)
+    K_cpu, W_cpu = max(1, min(K, 64)), 1
+    tps, cores, desc, ms = cpu_decode_sample(model, ctx, sample, K_cpu, W_cpu, budget_s=60.0)
+    K_cpu = int(desc.split(" decode step")[0])   # steps actually timed within the budget
     line = {"impl": "reference", "metric": "decode_tokens_per_s", "value": round(tps, 2), "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": K_cpu, "warmup": W_cpu, "ms_per_step": round(ms, 2), "higher_is_better": True,
             "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",

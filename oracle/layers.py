@@ -197,8 +197,8 @@ def silu_and_mul(x):
 def linear(x, w, out_bf16=True):
     """LinearBase::forward, linear.rs:228-239,354-356,437-439; ParallelLMHead::compute_logits,
     embed_head.rs:292-306: y = x . W^T (bf16 inputs, f32 accumulate)."""
-    y = np.matmul(x.astype(np.float32), w.astype(np.float32).T)
-    return round_bf16(y) if out_bf16 else y.astype(np.float32)
+    y = np.matmul(np.asarray(x, dtype=np.float32), np.asarray(w, dtype=np.float32).T)  # no copy of f32 weights
+    return round_bf16(y) if out_bf16 else np.asarray(y, dtype=np.float32)
 
 
 def embedding(table, ids):
