@@ -157,6 +157,48 @@ def cpu_decode_sample(model, ctx, sample_seqs, steps, warmup, budget_s=None):
     return tps, cores, desc, sum(times) / len(times) * 1e3
 
 
+def tensor_kernels(peak_tflops):
+    """Secondary rooflines (north_star (c)): the tensor-core kernels of the workload's PREFILL step, timed live with CUDA
+    events on torch's stream at the shapes of configs[1] (64 sequences x 512 tokens per prefill step of Qwen3-0.6B).
+    Returns None on any failure — the headline line never depends on it."""
+    try:
+        import torch
+        from nano_vllm_rs_b200 import ops
+
+        def ms_of(fn, iters=10):
+            for _ in range(3):
+                fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record(); torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / iters
+        out = {}
+        B, L, H, Hkv, D = 64, 512, 16, 8, 128
+        q = torch.randn((B * L, H, D), device="cuda").to(torch.bfloat16)
+        k = torch.randn((B * L, Hkv, D), device="cuda").to(torch.bfloat16)
+        v = torch.randn((B * L, Hkv, D), device="cuda").to(torch.bfloat16)
+        cu = torch.arange(0, B * L + 1, L, dtype=torch.int32, device="cuda")
+        o = torch.empty_like(q)
+        ms = ms_of(lambda: ops.varlen_prefill_attention(q, k, v, cu, cu, L, L, out=o))
+        tf = 4.0 * H * D * B * (L * (L + 1) / 2) / ms / 1e9
+        out["prefill_attention"] = {"shape": "64 x 512 tokens, 16/8 heads, causal", "ms": round(ms, 4), "achieved": round(tf, 1),
+                                    "peak": peak_tflops, "unit": "TFLOP/s", "frac": round(tf / peak_tflops, 4)}
+        M, N, K = B * L, 6144, 1024                                  # gate_up projection of the prefill step
+        x = torch.randn((M, K), device="cuda").to(torch.bfloat16)
+        w = (torch.randn((N, K), device="cuda") * 0.02).to(torch.bfloat16)
+        y = torch.empty((M, N), dtype=torch.bfloat16, device="cuda")
+        ms = ms_of(lambda: ops.gemm_bf16(x, w, out=y))
+        tf = 2.0 * M * N * K / ms / 1e9
+        out["prefill_gemm"] = {"shape": f"{M} x {N} x {K}", "ms": round(ms, 4), "achieved": round(tf, 1), "peak": peak_tflops,
+                               "unit": "TFLOP/s", "frac": round(tf / peak_tflops, 4)}
+        return out
+    except Exception as ex:  # noqa: BLE001
+        return {"error": str(ex)[:200]}
+
+
 def workload(args):
     model = args.model or ("qwen3-0.6b" if args.gpus == 1 else "qwen3-8b")
     wl = dict(MODELS[model])
@@ -332,6 +374,12 @@ def main():
                             "cycling through the layers' KV caches"},
         "clocks": clocks,
     }
+    if world == 1:
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("bf16_tflops", 1657.6)
+        except Exception:
+            pk = 1657.6
+        line["tensor_kernels"] = tensor_kernels(pk)
     if world == 1 and not args.no_cpu_baseline:
         ctx_mid = (ctx_first + ctx_last) // 2
         tps, cores, desc, _ = cpu_decode_sample(model, ctx_mid, 16, 2, 1)
