@@ -16,4 +16,6 @@ tokens.  What it does pin, and what tests/test_oracle_*.py check this oracle aga
     greedy argmax (attention.rs:456-497, rotary_embedding.rs:322-386, layernorm.rs:195-221,
     activation.rs:264-290, sampler.rs:333-342).
 Floating-point outputs (attention, logits, tokens) are therefore "parity unpinned" by the reference itself;
-they are additionally cross-checked against an independent torch-CPU implementation (tests/golden/)."""
+they are additionally cross-checked against independent implementations: torch-CPU layer math (tests/golden/layers.json)
+and, end to end (prefill + decode steps over the paged cache), Hugging Face transformers' Qwen3ForCausalLM in fp32
+(tests/golden/qwen3_hf.json, tests/test_oracle_model.py: within 0.04 sigma = bf16 rounding noise)."""
