@@ -19,6 +19,9 @@ CFG = dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_l
 SEED, STD = 20261104, 0.05
 PROMPTS = [[5, 17, 900, 3, 44], [1023, 0, 7, 7, 512, 64, 33, 2, 81, 300, 11, 640]]
 FORCED = [[10, 20, 30], [700, 5, 999]]   # tokens appended at the three decode steps (teacher forcing)
+# prefix caching: two prompts sharing a 32-token prefix (= 2 full blocks of 16), different suffixes
+PREFIX = [(i * 37 + 11) % 1024 for i in range(32)]
+SUFFIXES = [[3, 1, 4, 1, 5], [9, 2, 6, 5, 3, 5, 8, 9, 7]]
 
 
 def make_weights():
@@ -57,6 +60,10 @@ def main():
             if step < len(FORCED[0]):
                 for s, f in zip(seqs, FORCED):
                     s.append(f[step])
+    with torch.no_grad():
+        out["prefix"] = {"prefix": PREFIX, "suffixes": SUFFIXES,
+                         "logits": [[float(x) for x in model(torch.tensor([PREFIX + sfx])).logits[0, -1].double().numpy()]
+                                    for sfx in SUFFIXES]}
     json.dump(out, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "qwen3_hf.json"), "w"))
     print("wrote qwen3_hf.json", len(out["steps"]), "steps")
 

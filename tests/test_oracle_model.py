@@ -68,3 +68,28 @@ def test_wiring_errors_would_be_caught():
     logits = oracle.forward(H.prepare_prefill([s], bs))
     ref = np.asarray(GOLD["steps"][0][1])
     assert np.abs(logits[0] - ref).max() / ref.std() > 0.3
+
+
+def test_oracle_prefix_cached_prefill_matches_hf_full_recompute():
+    """SURVEY.md §8 a5 (flash_attention_varlen_with_cache, attention.rs:211-222): the second prompt shares two full blocks
+    with the first; the scheduler's prefix cache hits them, only the suffix is computed (bottom-right causal mask over the
+    paged prefix), and the logits equal HF's full recompute of the whole prompt."""
+    cfg = dict(GOLD["config"], qk_norm=True)
+    bs = 16
+    oracle = Q.Qwen3Oracle(cfg, _weights(), num_blocks=16, block_size=bs)
+    sched = H.Scheduler(H.Config(kvcache_block_size=bs, num_kvcache_blocks=16, max_num_batched_tokens=256, max_num_seqs=8))
+    pre, sfx = GOLD["prefix"]["prefix"], GOLD["prefix"]["suffixes"]
+    for i in range(2):                      # one prompt per prefill step so that the second one finds the blocks cached
+        s = H.Sequence(pre + sfx[i], H.SamplingParams(temperature=0.0, max_tokens=8, ignore_eos=True), block_size=bs)
+        sched.add_sequence(s)
+        batch, is_prefill = sched.schedule()
+        assert is_prefill and len(batch) == 1
+        inp = H.prepare_prefill(batch, bs)
+        if i == 1:
+            assert s.num_cached_tokens == 32 and inp.block_tables is not None and len(inp.input_ids) == len(sfx[1])
+        logits = oracle.forward(inp)
+        ref = np.asarray(GOLD["prefix"]["logits"][i])
+        sig = ref.std()
+        tol = LOGIT_SIGMA_PER_SQRT_LAYER * np.sqrt(cfg["num_hidden_layers"]) * sig + LOGIT_RTOL * np.abs(ref)
+        assert (np.abs(logits[0] - ref) <= tol).all(), (i, np.abs(logits[0] - ref).max() / sig)
+        sched.postprocess(batch, [1])
