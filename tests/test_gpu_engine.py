@@ -214,3 +214,37 @@ def test_engine_facade_stream_outputs_stats(cuda):
         eng3.add_request([1])
     with pytest.raises(ValueError):
         E.LLMEngine(cfg, std=0.05).add_request("needs a tokenizer")
+
+
+@pytest.mark.xfail(strict=False, reason="added after the round's GPU budget was spent: first GPU run pending (an XPASS is the "
+                                        "expected outcome; every link of the chain is validated separately)")
+def test_gpu_engine_vs_hf_transformers_golden(cuda):
+    """The GPU engine against an INDEPENDENT implementation directly: weights of tests/golden/qwen3_hf.json (non-unit norm
+    weights) loaded through nvllm_runner_load_weight, prefill + three teacher-forced decode steps, logits vs Hugging Face
+    transformers' Qwen3ForCausalLM (fp32).  Tolerance: GPU-vs-oracle plus oracle-vs-HF rounding noise (2 x the usual bound)."""
+    import importlib.util, json, os
+    from nano_vllm_rs_b200 import engine as E
+    from oracle.bf16 import f32_to_bf16_bits
+    here = os.path.dirname(os.path.abspath(__file__))
+    gold = json.load(open(os.path.join(here, "golden", "qwen3_hf.json")))
+    spec = importlib.util.spec_from_file_location("mk", os.path.join(here, "golden", "make_qwen3_hf_golden.py"))
+    mk = importlib.util.module_from_spec(spec); spec.loader.exec_module(mk)
+    cfg = E.Config("tiny", kvcache_block_size=16, num_kvcache_blocks=16).validate()
+    sched, runner = E.Scheduler(cfg), E.ModelRunner(cfg)
+    for name, a in mk.make_weights().items():
+        runner.load_weight(name, f32_to_bf16_bits(a))
+    n_dec = len(gold["forced"][0])
+    for p in gold["prompts"]:
+        sched.add_sequence(p, E.SamplingParams(temperature=0.0, max_tokens=n_dec + 1, ignore_eos=True))
+    worst = 0.0
+    for step in range(n_dec + 1):
+        b = sched.schedule()
+        toks, logits = runner.execute_model(b, return_logits=True)
+        ref = np.asarray(gold["steps"][step])
+        sig = ref.std(axis=-1, keepdims=True)
+        tol = 2 * LOGIT_SIGMA_PER_SQRT_LAYER * np.sqrt(2) * sig + LOGIT_RTOL * np.abs(ref)
+        err = np.abs(logits - ref)
+        worst = max(worst, float((err / sig).max()))
+        assert (err <= tol).all(), f"step {step}: GPU vs HF off by {(err / sig).max():.4f} sigma"
+        sched.postprocess([f[step] if step < n_dec else 0 for f in gold["forced"]])
+    print("max |GPU - HF| =", worst, "sigma")
