@@ -45,6 +45,9 @@ int nvllm_version(void);
 const char* nvllm_last_error(void);
 /* 1 when a CUDA device of compute capability 10.x is visible, else 0 (never throws). */
 int nvllm_device_ok(void);
+/* The NVLLM_* environment knobs (A/B measurement switches) are parsed once per process, never on a
+ * dispatch path; benchmark tools that sweep a knob inside one process call this after changing the environment. */
+int nvllm_reload_env(void);
 
 /* ------------------------------------------------------------------------------------------------
  * KV-cache layout descriptor.  The reference allocates each per-layer cache as

@@ -89,7 +89,10 @@ typedef struct nvllm_batch {
 typedef struct nvllm_scheduler nvllm_scheduler;
 int nvllm_scheduler_create(nvllm_scheduler** s, const nvllm_config* cfg);
 int nvllm_scheduler_destroy(nvllm_scheduler* s);
-/* Scheduler::add_sequence(Sequence::new(prompt, params)); returns the sequence id (>= 0) or a negative error. */
+/* Scheduler::add_sequence(Sequence::new(prompt, params)); returns the sequence id (>= 0) or a negative error.
+ * Admission bounds the reference never enforces (config.rs:27,60 carry max_model_len, nothing reads it): a prompt longer
+ * than max_model_len or than max_num_batched_tokens is refused with NVLLM_ERR_ARG before any state changes, and
+ * max_tokens is clamped to max_model_len - n + 1 so no sequence can outgrow the runner's block tables. */
 int64_t nvllm_scheduler_add_sequence(nvllm_scheduler* s, const int64_t* h_prompt, int32_t n,
                                      const nvllm_sampling_params* sp);
 int nvllm_scheduler_is_finished(const nvllm_scheduler* s);
@@ -111,6 +114,10 @@ int32_t nvllm_scheduler_free_list(const nvllm_scheduler* s, int32_t* h_out, int3
  * 2 Finished, 3 Preempted. */
 int32_t nvllm_scheduler_sequence(const nvllm_scheduler* s, int64_t seq_id, int64_t* h_tokens, int32_t cap,
                                  int32_t* num_prompt_tokens, int32_t* status);
+
+/* Frees the storage of a FINISHED sequence and recycles its slot (the reference returns finished sequences to the caller
+ * and drops them, llm_engine.rs:186-193).  Its id is never reused; nvllm_scheduler_sequence returns -1 for it afterwards. */
+int nvllm_scheduler_release_sequence(nvllm_scheduler* s, int64_t seq_id);
 
 /* ModelRunner (model_runner.rs:19-448) + Qwen3Model (models/qwen3.rs): device weights (this rank's TP shard),
  * per-layer paged KV cache, activation buffers, decode CUDA graphs per batch-size bucket. */

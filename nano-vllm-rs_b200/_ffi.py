@@ -38,6 +38,7 @@ PROTOTYPES = {
     "nvllm_version": (i32, []),
     "nvllm_last_error": (C.c_char_p, []),
     "nvllm_device_ok": (i32, []),
+    "nvllm_reload_env": (i32, []),
     "nvllm_store_kvcache": (i32, [vp, vp, vp, vp, vp, i32, i64, LP, i32, vp]),
     "nvllm_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "nvllm_paged_decode_choose_splits": (i32, [i32, i32, i32, i32]),

@@ -27,13 +27,38 @@ int sm_count() {
   return n;
 }
 
-bool pdl_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("NVLLM_PDL");
-    v = (e && e[0] == '0') ? 0 : 1;
+static Knobs g_knobs;
+static std::once_flag g_knobs_once;
+
+static void parse_knobs() {
+  Knobs k;
+  auto num = [](const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && e[0]) ? atoi(e) : dflt;
+  };
+  k.pdl = num("NVLLM_PDL", 1) != 0;
+  k.gemm_bn = num("NVLLM_GEMM_BN", 0);
+  k.gemm_2cta = num("NVLLM_GEMM_2CTA", 1);
+  k.gemm_mcast = num("NVLLM_GEMM_MCAST", 0) == 1;
+  k.gemm_stages = num("NVLLM_GEMM_STAGES", 0);
+  k.sk_stages = num("NVLLM_GEMM_SK_STAGES", 0);
+  if (const char* e = getenv("NVLLM_GEMM_SPLITK")) {
+    int bn = 0, sk = 0;
+    if (e[0] == '0' && e[1] == 0) k.splitk_mode = 0;
+    else if (sscanf(e, "%d,%d", &bn, &sk) == 2) { k.splitk_mode = 2; k.splitk_bn = bn; k.splitk_sk = sk; }
   }
-  return v == 1;
+  k.decode_cfg = num("NVLLM_DECODE_CFG", 0);
+  k.prefill_poly = num("NVLLM_PREFILL_POLY", 4);
+  k.fuse_rope = num("NVLLM_FUSE_ROPE", 0) == 1;
+  k.fused_tp = num("NVLLM_FUSED_TP", 1);
+  k.profile = num("NVLLM_PROFILE", 0);
+  if (const char* e = getenv("NVLLM_COMM_TIMEOUT_MS")) { const long long v = atoll(e); if (v > 0) k.comm_timeout_ms = v; }
+  g_knobs = k;
+}
+
+const Knobs& knobs() {
+  std::call_once(g_knobs_once, parse_knobs);
+  return g_knobs;
 }
 
 }  // namespace nvllm
@@ -41,6 +66,12 @@ bool pdl_enabled() {
 extern "C" {
 
 int nvllm_version(void) { return NVLLM_VERSION; }
+
+int nvllm_reload_env(void) {
+  nvllm::knobs();        // make sure the one-time parse has happened, then overwrite (single caller: benchmark tools)
+  nvllm::parse_knobs();
+  return 0;
+}
 
 const char* nvllm_last_error(void) { return nvllm::g_err; }
 

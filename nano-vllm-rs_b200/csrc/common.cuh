@@ -6,6 +6,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <mutex>
+
 #include "../../include/nvllm.h"
 
 // ------------------------------------------------------------------------------------------------
@@ -44,7 +46,37 @@ inline int cuda_status(cudaError_t e, const char* what) {
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 int sm_count();  // api.cu (cached)
-bool pdl_enabled();  // api.cu: NVLLM_PDL=0 disables programmatic dependent launch (A/B measurements)
+
+// The NVLLM_* environment knobs (A/B measurements), parsed ONCE per process — never on a dispatch
+// path.  nvllm_reload_env() (benchmark tools that sweep knobs inside one process) re-parses them.
+struct Knobs {
+  int pdl = 1;              // NVLLM_PDL: 0 disables programmatic dependent launch
+  int gemm_bn = 0;          // NVLLM_GEMM_BN: forced tile width (0 = heuristic)
+  int gemm_2cta = 1;        // NVLLM_GEMM_2CTA: 0 never, 1 default (M > 512), 2 every M > 128
+  int gemm_mcast = 0;       // NVLLM_GEMM_MCAST: 1 enables the x-multicast clusters
+  int gemm_stages = 0;      // NVLLM_GEMM_STAGES: ring depth cap of single-wave launches (0 = deepest)
+  int sk_stages = 0;        // NVLLM_GEMM_SK_STAGES: ring depth of the split-K kernel (0 = deepest)
+  int splitk_mode = 1;      // NVLLM_GEMM_SPLITK: 0 never, 1 cost model, 2 forced (splitk_bn, splitk_sk)
+  int splitk_bn = 0, splitk_sk = 0;
+  int decode_cfg = 0;       // NVLLM_DECODE_CFG: alternative (stages, warps) instantiations of the paged decode kernel
+  int prefill_poly = 4;     // NVLLM_PREFILL_POLY: exp2 split of the prefill softmax
+  int fuse_rope = 0;        // NVLLM_FUSE_ROPE: qkv GEMM epilogue with q/k-norm + RoPE + KV store
+  int fused_tp = 1;         // NVLLM_FUSED_TP: 0 = ncclAllReduce + separate add_rmsnorm
+  int profile = 0;          // NVLLM_PROFILE: 1 = the runner times every launch of eager steps with CUDA events
+  long long comm_timeout_ms = 600000;  // NVLLM_COMM_TIMEOUT_MS: peer-flag spin bound of the fused TP kernels
+};
+const Knobs& knobs();  // api.cu
+inline bool pdl_enabled() { return knobs().pdl != 0; }
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) exactly once per kernel instantiation, safe under concurrent callers
+// (the header promises re-entrancy).  Use inside a function that returns the C-ABI status code.
+#define NVLLM_SMEM_ATTR_ONCE(kern, bytes)                                                                     \
+  do {                                                                                                        \
+    static std::once_flag _once;                                                                              \
+    static cudaError_t _once_err = cudaSuccess;                                                               \
+    std::call_once(_once, [&] { _once_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); }); \
+    NVLLM_CUDA(_once_err);                                                                                    \
+  } while (0)
 
 }  // namespace nvllm
 

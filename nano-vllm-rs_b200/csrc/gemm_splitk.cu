@@ -244,8 +244,7 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
 template <int BN>
 int splitk_stages(int kb_per) {
   using C = SkCfg<BN>;
-  const char* e = getenv("NVLLM_GEMM_SK_STAGES");
-  int want = e ? atoi(e) : C::kMaxStages;
+  int want = knobs().sk_stages > 0 ? knobs().sk_stages : C::kMaxStages;
   if (want < 2) want = 2;
   if (want > C::kMaxStages) want = C::kMaxStages;
   return want < kb_per ? want : (kb_per < 1 ? 1 : kb_per);
@@ -256,11 +255,7 @@ int launch_splitk(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, 
                   int num_m_tiles, cudaStream_t st) {
   using C = SkCfg<BN>;
   auto kern = gemm_splitk_kernel<BN, SK, SILU>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::smem_bytes(C::kMaxStages)));
-    attr_set = true;
-  }
+  NVLLM_SMEM_ATTR_ONCE(kern, C::smem_bytes(C::kMaxStages));
   const int stages = splitk_stages<BN>((K / C::BK) / SK);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(tiles * SK);
@@ -293,8 +288,8 @@ long splitk_cost(int bn, int sk, int k) {
 // when no split-K configuration beats the single-CTA tile `bn_default` by a clear margin.  NVLLM_GEMM_SPLITK:
 // "0" = never, "BN,SK" = force that configuration where it is legal, unset / "1" = the cost model below.
 bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_bn, int* out_sk) {
-  const char* e = getenv("NVLLM_GEMM_SPLITK");
-  if (e && e[0] == '0' && e[1] == 0) return false;
+  const Knobs& kn = knobs();
+  if (kn.splitk_mode == 0) return false;
   if (m > 512 || k % 64 != 0) return false;  // up to four 128-row tile rows (the TP decode batches of 512 sequences)
   const int sms = sm_count();
   const int mt = (m + 127) / 128, num_kb = k / 64;
@@ -303,8 +298,8 @@ bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_
     if ((silu ? bn / (2 * sk) : bn / sk) < 8 || (bn == 64 && sk == 8)) return false;
     return static_cast<long>(mt) * (n_acc / bn) * sk <= sms;
   };
-  int fbn = 0, fsk = 0;
-  if (e && sscanf(e, "%d,%d", &fbn, &fsk) == 2) {
+  if (kn.splitk_mode == 2) {
+    const int fbn = kn.splitk_bn, fsk = kn.splitk_sk;
     const bool known = (fbn == 64 || fbn == 128 || fbn == 256) && (fsk == 2 || fsk == 4 || fsk == 8);
     if (known && legal(fbn, fsk)) { *out_bn = fbn; *out_sk = fsk; return true; }
     return false;

@@ -325,11 +325,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
                        cudaStream_t st, const RopeEpi& re = RopeEpi{}) {
   using C = GemmCfg<BN>;
   auto kern = gemm_tcgen05_kernel<BN, OutT, SILU, CN, ROPE>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    attr_set = true;
-  }
+  NVLLM_SMEM_ATTR_ONCE(kern, C::kSmemBytes);
   const int num_m_tiles = (M + C::BM - 1) / C::BM;
   const int num_n_tiles = SILU ? (N + BN / 2 - 1) / (BN / 2) : (N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * (num_n_tiles / CN);  // cluster tiles (the caller guarantees num_n_tiles % CN == 0)
@@ -340,8 +336,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
   // while this kernel's are still running.
   int stages = C::kStages;
   if (CN == 1 && num_tiles <= max_clusters) {
-    const char* e = getenv("NVLLM_GEMM_STAGES");
-    const int want = e ? atoi(e) : 0;
+    const int want = knobs().gemm_stages;
     if (want >= 2 && want < stages) stages = want;
   }
   const int smem = C::kSmemBytes - (C::kStages - stages) * C::kStageBytes;
@@ -368,8 +363,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
 }
 
 static int pick_bn(int M, int N) {
-  const char* e = getenv("NVLLM_GEMM_BN");  // benchmarking knob, re-read per call so one process can sweep it
-  const int forced = e ? atoi(e) : 0;
+  const int forced = knobs().gemm_bn;  // benchmarking knob (nvllm_reload_env() lets one process sweep it)
   if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
   const int sms = sm_count();
   const long mt = (M + 127) / 128;
@@ -402,10 +396,7 @@ static bool use_2cta();
 // from L2 once per n-tile and also do better on single-CTA tiles until a split-K variant exists.
 static bool want_2cta(int m, int n, int k) {
   if (m <= 128 || !use_2cta()) return false;
-  {
-    const char* e = getenv("NVLLM_GEMM_2CTA");  // "2": benchmark knob, CTA pairs for every m > 128
-    if (e && e[0] == '2') return true;
-  }
+  if (knobs().gemm_2cta == 2) return true;  // benchmark knob: CTA pairs for every m > 128
   // In-graph measurements (profiles/r01_gemm_ingraph_v2_splitk.jsonl): at M = 512 (the TP decode batches) the single-CTA
   // kernel is 7-17 % faster on all four projections; CTA pairs pay off from two 256-row tile rows upwards (prefill).
   if (m <= 512) return false;
@@ -417,13 +408,11 @@ static bool use_mcast() {
   // x-multicast clusters: OFF by default.  In-graph they measured 5-7 % SLOWER than plain tiles on every shape they
   // apply to (the bytes still have to enter every SM; the bound is the SM's TMA ingest, not L2 reads) and the long-K
   // narrow-N projections they were built for now go to the cluster split-K kernel.  NVLLM_GEMM_MCAST=1 enables them.
-  const char* e = getenv("NVLLM_GEMM_MCAST");
-  return e && e[0] == '1';
+  return knobs().gemm_mcast != 0;
 }
 
 static bool use_2cta() {
-  const char* e = getenv("NVLLM_GEMM_2CTA");  // A/B knob: 0 keeps every shape on the single-CTA kernel
-  return !(e && e[0] == '0');
+  return knobs().gemm_2cta != 0;  // A/B knob: 0 keeps every shape on the single-CTA kernel
 }
 
 }  // namespace nvllm

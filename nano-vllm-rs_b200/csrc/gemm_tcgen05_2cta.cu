@@ -198,11 +198,7 @@ static int launch_gemm2(const CUtensorMap& tx, const CUtensorMap& tw, void* y, i
                         cudaStream_t st) {
   using C = Gemm2Cfg<BN>;
   auto kern = gemm_tcgen05_2cta_kernel<BN, OutT, SILU>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    attr_set = true;
-  }
+  NVLLM_SMEM_ATTR_ONCE(kern, C::kSmemBytes);
   const int num_m_tiles = (M + C::BM - 1) / C::BM;
   const int num_n_tiles = SILU ? (N + BN / 2 - 1) / (BN / 2) : (N + BN - 1) / BN;
   const int num_tiles = num_m_tiles * num_n_tiles;
@@ -247,8 +243,7 @@ static int pick_bn_2cta(int M, int N) {
 
 int gemm_2cta_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw,
                        int64_t ldy, int out_dtype, cudaStream_t st) {
-  const char* e = getenv("NVLLM_GEMM_BN");
-  const int forced = e ? atoi(e) : 0;
+  const int forced = knobs().gemm_bn;
   const int bn = (forced == 64 || forced == 128 || forced == 256) ? forced : pick_bn_2cta(m, n);
   CUtensorMap tx, tw;
   if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;

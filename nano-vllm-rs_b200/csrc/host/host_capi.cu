@@ -15,6 +15,9 @@ struct nvllm_scheduler {
 #define NVLLM_TRY(body)                         \
   try {                                         \
     body;                                       \
+  } catch (const std::invalid_argument& e) {    \
+    nvllm::set_error("%s", e.what());           \
+    return NVLLM_ERR_ARG;                       \
   } catch (const std::exception& e) {           \
     nvllm::set_error("%s", e.what());           \
     return NVLLM_ERR_STATE;                     \
@@ -65,6 +68,10 @@ int nvllm_config_validate(const nvllm_config* c) {
   // 16 and 4 (scheduler.rs:383, block_manager.rs:427); the kernels need a multiple of 16.
   NVLLM_CHECK_ARG(c->kvcache_block_size > 0 && c->kvcache_block_size % 16 == 0, NVLLM_ERR_ARG,
                   "KV cache block size must be a positive multiple of 16, got %d", c->kvcache_block_size);
+  // the paged-prefix prefill kernel walks the cache in 128-key tiles (prefill_attn.cu): a block must divide a tile or be
+  // a whole number of tiles — refused here, not at the first prefix-cached prefill with scheduler state already mutated
+  NVLLM_CHECK_ARG(c->kvcache_block_size >= 128 ? c->kvcache_block_size % 128 == 0 : 128 % c->kvcache_block_size == 0,
+                  NVLLM_ERR_ARG, "KV cache block size %d must divide 128 or be a multiple of 128", c->kvcache_block_size);
   NVLLM_CHECK_ARG(c->tensor_parallel_size >= 1 && c->tensor_parallel_size <= 8, NVLLM_ERR_ARG,
                   "Tensor parallel size must be between 1 and 8, got %d", c->tensor_parallel_size);  // config.rs:99-101
   NVLLM_CHECK_ARG(c->tp_rank >= 0 && c->tp_rank < c->tensor_parallel_size, NVLLM_ERR_ARG, "tp_rank %d", c->tp_rank);
@@ -81,7 +88,8 @@ int nvllm_config_validate(const nvllm_config* c) {
                   "Intermediate size must be divisible by tensor parallel size");
   NVLLM_CHECK_ARG(c->num_attention_heads % c->num_key_value_heads == 0, NVLLM_ERR_ARG,
                   "num_attention_heads must be a multiple of num_key_value_heads");
-  NVLLM_CHECK_ARG(c->head_dim == 64 || c->head_dim == 128, NVLLM_ERR_ARG, "head_dim %d not in {64,128}", c->head_dim);
+  // every Qwen3 named architecture has head_dim 128 and the tcgen05 prefill kernel is built for it (prefill_attn.cu)
+  NVLLM_CHECK_ARG(c->head_dim == 128, NVLLM_ERR_ARG, "head_dim %d is not supported by the engine (128 only)", c->head_dim);
   NVLLM_CHECK_ARG(c->hidden_size > 0 && c->hidden_size % 64 == 0 && (c->intermediate_size / tp) % 64 == 0 &&
                       c->vocab_size > 0 && c->vocab_size % (8 * tp) == 0 && c->num_hidden_layers > 0,
                   NVLLM_ERR_ARG, "hidden %% 64, (intermediate/tp) %% 64, vocab %% (8 tp) must hold");
@@ -157,13 +165,21 @@ int32_t nvllm_scheduler_free_list(const nvllm_scheduler* s, int32_t* h_out, int3
 }
 int32_t nvllm_scheduler_sequence(const nvllm_scheduler* s, int64_t seq_id, int64_t* h_tokens, int32_t cap,
                                  int32_t* num_prompt_tokens, int32_t* status) {
-  if (!s || seq_id < 0 || seq_id >= static_cast<int64_t>(s->impl.sequences().size())) return -1;
-  const auto& q = s->impl.sequences()[seq_id];
+  const nvllm::host::Sequence* qp = s ? s->impl.find(seq_id) : nullptr;
+  if (qp == nullptr) return -1;
+  const auto& q = *qp;
   if (num_prompt_tokens) *num_prompt_tokens = q.num_prompt_tokens;
   if (status) *status = static_cast<int32_t>(q.status);
   if (h_tokens)
     for (int32_t i = 0; i < q.len() && i < cap; ++i) h_tokens[i] = q.token_ids[i];
   return q.len();
+}
+
+int nvllm_scheduler_release_sequence(nvllm_scheduler* s, int64_t seq_id) {
+  NVLLM_CHECK_ARG(s, NVLLM_ERR_ARG, "release_sequence: NULL");
+  NVLLM_CHECK_ARG(s->impl.release(seq_id), NVLLM_ERR_STATE, "release_sequence: sequence %lld is unknown or not finished",
+                  (long long)seq_id);
+  return 0;
 }
 
 }  // extern "C"

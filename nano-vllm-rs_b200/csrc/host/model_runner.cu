@@ -109,6 +109,9 @@ struct nvllm_runner {
   int last_decode_b = 0, last_decode_splits = 1;
   std::vector<int32_t> last_ctx;
   bool weights_ready = false;
+  // load_weight bookkeeping: every tensor the architecture needs must have arrived before the first execute
+  // (a partially loaded checkpoint would otherwise run on uninitialised layer weights)
+  std::vector<uint32_t> loaded;  // per layer: bit mask of the 11 per-layer tensors; last entry: embed | lm_head | norm
   bool fuse_rope = false; // NVLLM_FUSE_ROPE=1: qkv GEMM epilogue does q/k norm + RoPE + KV store for decode-sized batches
   bool fused_tp = false;  // h / normed / proj live in NVLink-mapped symmetric memory; all-reduce fused with add + RMSNorm
 
@@ -182,7 +185,7 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   if (c.kv_layout == 1) { layout.token_stride = static_cast<int64_t>(Hkv) * D; layout.head_stride = D; }   // reference
   else { layout.token_stride = D; layout.head_stride = static_cast<int64_t>(bs) * D; }                     // head-major
 
-  { const char* e = getenv("NVLLM_FUSE_ROPE"); fuse_rope = e && e[0] == '1'; }
+  fuse_rope = knobs().fuse_rope != 0;
   NVLLM_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   // weights
   RUN(dalloc(&embed, static_cast<size_t>(vocab) * hidden));
@@ -211,8 +214,7 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   // activations
   const size_t T = max_tokens;
   if (tp > 1) {
-    const char* e = getenv("NVLLM_FUSED_TP");  // A/B knob: 0 = ncclAllReduce + separate add_rmsnorm
-    if (!(e && e[0] == '0')) {
+    if (knobs().fused_tp != 0) {  // A/B knob NVLLM_FUSED_TP=0: ncclAllReduce + separate add_rmsnorm
       const size_t one = (T * hidden * 2 + 255) & ~static_cast<size_t>(255);
       void* base = nullptr;
       if (nvllm_comm_symm_alloc(comm, 3 * one, &base) == 0) {
@@ -313,16 +315,26 @@ int nvllm_runner::load_weight(const char* name_c, const void* src, int64_t rows,
     NVLLM_CUDA(cudaStreamSynchronize(stream));
     return 0;
   };
-  if (name == "model.embed_tokens.weight") {
-    RUN(slice(embed, vocab, hidden, 0, vocab, 0, hidden));
-    weights_ready = true;
+  if (loaded.empty()) loaded.assign(layers + 1, 0u);
+  // marks tensor `bit` of group `grp` as present and re-evaluates completeness
+  auto done = [&](int rc, int grp, int bit) -> int {
+    if (rc != 0) return rc;
+    loaded[grp] |= 1u << bit;
+    const uint32_t top = cfg.tie_word_embeddings ? 0x5u : 0x7u;  // embed | [lm_head] | norm
+    bool all = (loaded[layers] & top) == top;
+    const uint32_t need = cfg.qk_norm ? 0x7ffu : 0x7f3u;
+    for (int l = 0; l < layers && all; ++l) all = (loaded[l] & need) == need;
+    weights_ready = all;
     return 0;
-  }
+  };
+  if (name == "model.embed_tokens.weight") return done(slice(embed, vocab, hidden, 0, vocab, 0, hidden), layers, 0);
   if (name == "lm_head.weight") {
-    NVLLM_CHECK_ARG(!cfg.tie_word_embeddings, NVLLM_ERR_STATE, "load_weight: lm_head is tied to the embedding");
-    return slice(lm_head, vocab, hidden, static_cast<int64_t>(rank) * vshard, vshard, 0, hidden);
+    // tied checkpoints often ship lm_head.weight as a copy of the embedding: the engine reads the head out of the
+    // embedding table in that case (create()), so the tensor is accepted and ignored instead of aborting the load
+    if (cfg.tie_word_embeddings) return 0;
+    return done(slice(lm_head, vocab, hidden, static_cast<int64_t>(rank) * vshard, vshard, 0, hidden), layers, 1);
   }
-  if (name == "model.norm.weight") return slice(final_norm, 1, hidden, 0, 1, 0, hidden);
+  if (name == "model.norm.weight") return done(slice(final_norm, 1, hidden, 0, 1, 0, hidden), layers, 2);
   const std::string pre = "model.layers.";
   NVLLM_CHECK_ARG(name.compare(0, pre.size(), pre) == 0, NVLLM_ERR_ARG, "load_weight: unknown tensor '%s'", name_c);
   const size_t dot = name.find('.', pre.size());
@@ -332,17 +344,17 @@ int nvllm_runner::load_weight(const char* name_c, const void* src, int64_t rows,
   const std::string rest = name.substr(dot + 1);
   LayerWeights& w = lw[l];
   const int64_t HD = static_cast<int64_t>(H) * D, KD = static_cast<int64_t>(Hkv) * D;
-  if (rest == "input_layernorm.weight") return slice(w.input_ln, 1, hidden, 0, 1, 0, hidden);
-  if (rest == "post_attention_layernorm.weight") return slice(w.post_ln, 1, hidden, 0, 1, 0, hidden);
-  if (rest == "self_attn.q_norm.weight") return slice(w.q_norm, 1, D, 0, 1, 0, D);
-  if (rest == "self_attn.k_norm.weight") return slice(w.k_norm, 1, D, 0, 1, 0, D);
-  if (rest == "self_attn.q_proj.weight") return slice(w.qkv, static_cast<int64_t>(Hf) * D, hidden, rank * HD, HD, 0, hidden);
-  if (rest == "self_attn.k_proj.weight") return slice(w.qkv + HD * hidden, static_cast<int64_t>(Hkvf) * D, hidden, rank * KD, KD, 0, hidden);
-  if (rest == "self_attn.v_proj.weight") return slice(w.qkv + (HD + KD) * hidden, static_cast<int64_t>(Hkvf) * D, hidden, rank * KD, KD, 0, hidden);
-  if (rest == "self_attn.o_proj.weight") return slice(w.o, hidden, static_cast<int64_t>(Hf) * D, 0, hidden, rank * HD, HD);
-  if (rest == "mlp.gate_proj.weight") return slice(w.gate_up, If, hidden, static_cast<int64_t>(rank) * inter, inter, 0, hidden);
-  if (rest == "mlp.up_proj.weight") return slice(w.gate_up + static_cast<int64_t>(inter) * hidden, If, hidden, static_cast<int64_t>(rank) * inter, inter, 0, hidden);
-  if (rest == "mlp.down_proj.weight") return slice(w.down, hidden, If, 0, hidden, static_cast<int64_t>(rank) * inter, inter);
+  if (rest == "input_layernorm.weight") return done(slice(w.input_ln, 1, hidden, 0, 1, 0, hidden), l, 0);
+  if (rest == "post_attention_layernorm.weight") return done(slice(w.post_ln, 1, hidden, 0, 1, 0, hidden), l, 1);
+  if (rest == "self_attn.q_norm.weight") return done(slice(w.q_norm, 1, D, 0, 1, 0, D), l, 2);
+  if (rest == "self_attn.k_norm.weight") return done(slice(w.k_norm, 1, D, 0, 1, 0, D), l, 3);
+  if (rest == "self_attn.q_proj.weight") return done(slice(w.qkv, static_cast<int64_t>(Hf) * D, hidden, rank * HD, HD, 0, hidden), l, 4);
+  if (rest == "self_attn.k_proj.weight") return done(slice(w.qkv + HD * hidden, static_cast<int64_t>(Hkvf) * D, hidden, rank * KD, KD, 0, hidden), l, 5);
+  if (rest == "self_attn.v_proj.weight") return done(slice(w.qkv + (HD + KD) * hidden, static_cast<int64_t>(Hkvf) * D, hidden, rank * KD, KD, 0, hidden), l, 6);
+  if (rest == "self_attn.o_proj.weight") return done(slice(w.o, hidden, static_cast<int64_t>(Hf) * D, 0, hidden, rank * HD, HD), l, 7);
+  if (rest == "mlp.gate_proj.weight") return done(slice(w.gate_up, If, hidden, static_cast<int64_t>(rank) * inter, inter, 0, hidden), l, 8);
+  if (rest == "mlp.up_proj.weight") return done(slice(w.gate_up + static_cast<int64_t>(inter) * hidden, If, hidden, static_cast<int64_t>(rank) * inter, inter, 0, hidden), l, 9);
+  if (rest == "mlp.down_proj.weight") return done(slice(w.down, hidden, If, 0, hidden, static_cast<int64_t>(rank) * inter, inter), l, 10);
   NVLLM_CHECK_ARG(false, NVLLM_ERR_ARG, "load_weight: unknown tensor '%s'", name_c);
 }
 
@@ -492,7 +504,8 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
 }
 
 int nvllm_runner::execute_async(const nvllm_batch& b) {
-  NVLLM_CHECK_ARG(weights_ready, NVLLM_ERR_STATE, "execute: weights not initialised (init_weights / load_weight)");
+  NVLLM_CHECK_ARG(weights_ready, NVLLM_ERR_STATE,
+                  "execute: weights not initialised (init_weights, or load_weight for EVERY tensor of the architecture)");
   NVLLM_CHECK_ARG(b.num_seqs > 0 && b.num_tokens > 0, NVLLM_ERR_ARG, "execute: empty batch");
   bool sampled = false;
   for (int i = 0; i < b.num_seqs && b.temperatures != nullptr; ++i) sampled |= b.temperatures[i] != 0.0f;
@@ -709,7 +722,8 @@ extern "C" {
 
 int nvllm_engine_create(nvllm_engine** e, const nvllm_config* cfg, nvllm_comm* comm) {
   NVLLM_CHECK_ARG(e && cfg, NVLLM_ERR_ARG, "engine_create: NULL");
-  nvllm_engine* p = new nvllm_engine();
+  nvllm_engine* p = nullptr;
+  NVLLM_TRY_NEW(p, new nvllm_engine());
   int rc = nvllm_scheduler_create(&p->sched, cfg);
   if (rc == 0) rc = nvllm_runner_create(&p->runner, cfg, comm);
   if (rc != 0) {

@@ -22,26 +22,57 @@ class Scheduler {
  public:
   explicit Scheduler(const nvllm_config& c)
       : max_num_seqs_(c.max_num_seqs), max_num_batched_tokens_(c.max_num_batched_tokens),
-        eos_(c.eos_token_id), block_size_(c.kvcache_block_size),
+        max_model_len_(c.max_model_len), eos_(c.eos_token_id), block_size_(c.kvcache_block_size),
         bm_(c.num_kvcache_blocks > 0 ? c.num_kvcache_blocks : 1000, c.kvcache_block_size) {}  // :71-74
 
   BlockManager& block_manager() { return bm_; }
   const BlockManager& block_manager() const { return bm_; }
   bool is_finished() const { return waiting_.empty() && running_.empty(); }                   // :88-90
-  const std::vector<Sequence>& sequences() const { return seqs_; }
+  // Sequence by id, or nullptr once it has been released (or never existed).
+  const Sequence* find(int64_t seq_id) const {
+    auto it = id_to_slot_.find(seq_id);
+    return it == id_to_slot_.end() ? nullptr : &seqs_[it->second];
+  }
 
+  // Admission limits the reference never checks (it carries max_model_len, config.rs:27,60, but nothing reads it): the
+  // runner sizes its block tables and RoPE table for max_model_len tokens, so a request that could outgrow them is
+  // bounded HERE, before any scheduler state changes.  A prompt longer than max_model_len (or than one prefill batch,
+  // which would never be admitted: scheduler.rs:136) is refused; max_tokens is clamped so the sequence stops with
+  // len == max_model_len + 1 at the latest (the last sampled token is never fed back, so it needs no KV slot).
   int64_t add_sequence(const int64_t* prompt, int32_t n, const nvllm_sampling_params& sp) {   // :93-98
+    if (max_model_len_ > 0 && n > max_model_len_)
+      throw std::invalid_argument("prompt of " + std::to_string(n) + " tokens exceeds max_model_len " + std::to_string(max_model_len_));
+    if (n > max_num_batched_tokens_)
+      throw std::invalid_argument("prompt of " + std::to_string(n) + " tokens exceeds max_num_batched_tokens " +
+                                  std::to_string(max_num_batched_tokens_));
     Sequence s;
-    s.seq_id = static_cast<int64_t>(seqs_.size());  // per-scheduler counter (reference: process-global AtomicU64)
+    s.seq_id = next_seq_id_++;  // per-scheduler counter (reference: process-global AtomicU64)
     s.token_ids.assign(prompt, prompt + n);
     s.last_token = n > 0 ? prompt[n - 1] : 0;
     s.num_prompt_tokens = n;
     s.sp = sp;
+    if (max_model_len_ > 0 && s.sp.max_tokens > max_model_len_ - n + 1) s.sp.max_tokens = max_model_len_ - n + 1;
     s.block_size = block_size_;
-    seqs_.push_back(std::move(s));
-    waiting_.push_back(static_cast<int32_t>(seqs_.size() - 1));
+    int32_t slot;
+    if (!free_slots_.empty()) { slot = free_slots_.back(); free_slots_.pop_back(); seqs_[slot] = std::move(s); }
+    else { slot = static_cast<int32_t>(seqs_.size()); seqs_.push_back(std::move(s)); }
+    id_to_slot_[seqs_[slot].seq_id] = slot;
+    waiting_.push_back(slot);
     ++total_sequences_;
-    return seqs_.back().seq_id;
+    return seqs_[slot].seq_id;
+  }
+
+  // Drops a FINISHED sequence's storage and recycles its slab slot (the reference hands finished sequences to the caller
+  // and forgets them, llm_engine.rs:186-193; without this a long-running engine grows without bound).
+  bool release(int64_t seq_id) {
+    auto it = id_to_slot_.find(seq_id);
+    if (it == id_to_slot_.end() || seqs_[it->second].status != Status::Finished) return false;
+    Sequence& s = seqs_[it->second];
+    std::vector<int64_t>().swap(s.token_ids);
+    std::vector<int32_t>().swap(s.block_table);
+    free_slots_.push_back(it->second);
+    id_to_slot_.erase(it);
+    return true;
   }
 
   // Scheduler::schedule (:103-116): prefill first, else decode.  Fills `out` (pointers into arrays_).
@@ -226,11 +257,14 @@ class Scheduler {
     fill_tables(out);
   }
 
-  int32_t max_num_seqs_, max_num_batched_tokens_;
+  int32_t max_num_seqs_, max_num_batched_tokens_, max_model_len_;
   int64_t eos_;
   int32_t block_size_;
   BlockManager bm_;
-  std::vector<Sequence> seqs_;           // slab: index == seq_id
+  std::vector<Sequence> seqs_;           // slab; queues hold slab indices, id_to_slot_ maps seq_id -> index
+  std::unordered_map<int64_t, int32_t> id_to_slot_;
+  std::vector<int32_t> free_slots_;      // slab entries of released sequences, reused by add_sequence
+  int64_t next_seq_id_ = 0;
   std::deque<int32_t> waiting_, running_;
   BatchArrays arrays_;
   int64_t total_sequences_ = 0, finished_ = 0, preemptions_ = 0, prefill_batches_ = 0, decode_batches_ = 0;

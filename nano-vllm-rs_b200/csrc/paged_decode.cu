@@ -309,11 +309,7 @@ template <int D, int STAGES, int NWARPS>
 static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
   using C = DecodeCfg<D, STAGES, NWARPS>;
   auto kern = paged_decode_kernel<D, STAGES, NWARPS>;
-  static bool attr_set = false;  // per instantiation; idempotent, so a race only repeats the call
-  if (!attr_set) {
-    NVLLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    attr_set = true;
-  }
+  NVLLM_SMEM_ATTR_ONCE(kern, C::kSmemBytes);
   dim3 grid(p.num_splits, p.Hkv * p.ngrp, p.batch);
   NVLLM_CUDA(launch_pdl(kern, grid, dim3(NWARPS * 32), C::kSmemBytes, stream, p));
   if (p.num_splits > 1)
@@ -322,14 +318,7 @@ static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
 }
 
 // Tuning knob for benchmarking only (bench.py --decode-cfg): 0 = default.
-static int decode_cfg_id() {
-  static int id = -1;
-  if (id < 0) {
-    const char* e = getenv("NVLLM_DECODE_CFG");
-    id = e ? atoi(e) : 0;
-  }
-  return id;
-}
+static int decode_cfg_id() { return knobs().decode_cfg; }
 
 }  // namespace nvllm
 

@@ -330,286 +330,6 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_con
   }
 }
 
-// ------------------------------------------------------------------------------------------------------------------
-// v5 (OPT-IN, NVLLM_PREFILL_V5=1; written at the end of round 1 without GPU time left to validate it — the default path
-// above is untouched): the same CTA / warp roles and TMEM budget, but the S -> softmax -> P -> PV chain runs on 64-key
-// SUB-TILES with S double-buffered per row group (TMEM per group: S0 64 | S1 64 | O 128 columns).  Motivation (ncu source
-// page of v4, profiles/r01_ncu_prefill_gemm.md): 34 % of the softmax warps' samples wait for S and the MMA thread spins on
-// p_ready — with P aliased over a single S buffer, S_{j+1} of a group cannot be issued before PV_j, so each group's chain is
-// strictly serial and only the OTHER group's work can fill the gaps.  Here S_{h+2} is issued right after PV_h into the
-// buffer PV_h has just drained, S_{h+1} is already in flight in the other buffer while softmax_h runs, and softmax_h only
-// synchronises with PV_{h-1} (for the rare O rescale) AFTER it has produced P_h.
-// ------------------------------------------------------------------------------------------------------------------
-namespace pf {
-constexpr int HN = 64;                               // keys per sub-tile
-constexpr int kNumBarsV5 = 1 + 2 * NSLOT + 4 + 4 + 2;  // q_full, slots, s_full[g][b], p_ready[g][b], o_done[g]
-constexpr int kSmemBytesV5 = kSmemBar + kNumBarsV5 * 8 + 16 + 1024;
-}  // namespace pf
-
-__global__ void __launch_bounds__(pf::kThreads, 1)
-prefill_attn_v5_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
-                       const __grid_constant__ CUtensorMap tmap_v, const PrefillParams p) {
-  using namespace pf;
-  pdl_launch_dependents();
-  pdl_wait();
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  const uint32_t bars = smem_base + kSmemBar;
-  const uint32_t q_full = bars;
-  auto slot_full = [&](int s) { return bars + (1 + s) * 8; };
-  auto slot_empty = [&](int s) { return bars + (1 + NSLOT + s) * 8; };
-  auto s_full = [&](int g, int b) { return bars + (1 + 2 * NSLOT + g * 2 + b) * 8; };       // S_h (h & 1 == b) is in TMEM
-  auto p_ready = [&](int g, int b) { return bars + (1 + 2 * NSLOT + 4 + g * 2 + b) * 8; };  // P_h is in TMEM (128 arrivals)
-  auto o_done = [&](int g) { return bars + (1 + 2 * NSLOT + 8 + g) * 8; };                  // PV_h has retired
-  const uint32_t tmem_slot = bars + kNumBarsV5 * 8;
-
-  const int seq = blockIdx.z, head = blockIdx.y;
-  const int qblk = gridDim.x - 1 - blockIdx.x;
-  const int kvh = head / (p.H / p.Hkv);
-  const int q0 = __ldg(p.cu_q + seq), Lq = __ldg(p.cu_q + seq + 1) - q0;
-  const int k0 = __ldg(p.cu_k + seq), Lk = __ldg(p.cu_k + seq + 1) - k0;
-  if (qblk * 2 * BM >= Lq) return;
-  const int shift = Lk - Lq;
-  auto subs_for = [&](int g) {  // number of 64-key sub-tiles a row group needs
-    const int first = qblk * 2 * BM + g * BM;
-    if (first >= Lq) return 0;
-    const int last = min(first + BM, Lq) - 1;
-    const int visible = max(1, min(Lk, shift + last + 1));
-    return (visible + HN - 1) / HN;
-  };
-  const int n_sub[2] = {subs_for(0), subs_for(1)};
-  const int max_sub = max(n_sub[0], n_sub[1]);
-  const int n_tiles = (max_sub + 1) / 2;  // 128-key K / V tiles to stream
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp == 8 && lane == 0) {
-    tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k); tma_prefetch_desc(&tmap_v);
-    mbar_init(q_full, 1);
-    for (int s = 0; s < NSLOT; ++s) { mbar_init(slot_full(s), 1); mbar_init(slot_empty(s), 1); }
-    for (int g = 0; g < 2; ++g) {
-      for (int b = 0; b < 2; ++b) { mbar_init(s_full(g, b), 1); mbar_init(p_ready(g, b), BM); }
-      mbar_init(o_done(g), 1);
-    }
-    fence_barrier_init();
-  }
-  if (warp == 0) tmem_alloc<512>(tmem_slot);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *reinterpret_cast<uint32_t*>(smem_gen + kSmemBar + kNumBarsV5 * 8);
-
-  if (warp >= 8) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
-  }
-  if (warp >= 10) {
-    // idle warps of the third warpgroup
-  } else if (warp == 8) {
-    if (lane == 0) {
-      // ===== TMA producer (as v4: Q once, then K_0, V_0, K_1, V_1, ... 128-key tiles) =====
-      mbar_expect_tx(q_full, 2 * kQBytes);
-      for (int g = 0; g < 2; ++g)
-        for (int hf = 0; hf < 2; ++hf)
-          tma_load_2d(smem_base + kSmemQ + g * kQBytes + hf * (BM * 128), &tmap_q, q_full, head * D + hf * 64,
-                      q0 + qblk * 2 * BM + g * BM);
-      const int32_t* table = p.tables ? p.tables + static_cast<int64_t>(seq) * p.max_blocks : nullptr;
-      for (int t = 0; t < 2 * n_tiles; ++t) {
-        const int j = t >> 1, slot = t % NSLOT;
-        const CUtensorMap* map = (t & 1) ? &tmap_v : &tmap_k;
-        mbar_wait(slot_empty(slot), ((t / NSLOT) & 1) ^ 1);
-        mbar_expect_tx(slot_full(slot), kTileBytes);
-        const uint32_t dst = smem_base + kSmemKV + slot * kTileBytes;
-        if (table == nullptr) {
-          for (int hf = 0; hf < 2; ++hf)
-            tma_load_2d(dst + hf * (BN * 128), map, slot_full(slot), kvh * D + hf * 64, k0 + j * BN);
-        } else {
-          for (int c = 0; c < BN / p.box_tok; ++c) {
-            const int tok = j * BN + c * p.box_tok;
-            const int bi = tok / p.block_size;
-            const int blk = bi < p.max_blocks ? __ldg(table + bi) : -1;
-            const int blk_c = blk < 0 ? 0x3fffff : blk;
-            for (int hf = 0; hf < 2; ++hf)
-              tma_load_4d(dst + hf * (BN * 128) + c * p.box_tok * 128, map, slot_full(slot), hf * 64,
-                          tok - bi * p.block_size, kvh, blk_c);
-          }
-        }
-      }
-    }
-  } else if (warp == 9) {
-    if (lane == 0) {
-      // ===== MMA issuer (both row groups), sub-tile h = 2 * (128-key tile) + half =====
-      constexpr uint32_t idesc_s = umma_idesc_bf16(BM, HN, 0, 0);  // S sub-tile: M128 N64
-      constexpr uint32_t idesc_o = umma_idesc_bf16(BM, D, 0, 1);   // P K-major (TMEM), V MN-major
-      int tiles_seen = -1;                                          // highest ring entry t already waited for
-      auto need_tile = [&](int t) {                                 // ring entries are consumed in increasing order
-        while (tiles_seen < t) { ++tiles_seen; mbar_wait(slot_full(tiles_seen % NSLOT), (tiles_seen / NSLOT) & 1); }
-        tc_fence_after();
-      };
-      auto issue_s = [&](int g, int h) {  // S_h^g = Q^g . K_h^T into S buffer h & 1
-        const uint32_t sQ = smem_base + kSmemQ + g * kQBytes;
-        const uint32_t sK = smem_base + kSmemKV + ((2 * (h >> 1)) % NSLOT) * kTileBytes + (h & 1) * (HN * 128);
-#pragma unroll
-        for (int ks = 0; ks < D / 16; ++ks) {
-          const uint64_t ad = umma_desc_sw128(sQ + (ks >> 2) * (BM * 128) + (ks & 3) * 32, 16, 1024);
-          const uint64_t bd = umma_desc_sw128(sK + (ks >> 2) * (BN * 128) + (ks & 3) * 32, 16, 1024);
-          umma_bf16_ss(tmem_base + g * 256 + (h & 1) * HN, ad, bd, idesc_s, ks != 0);
-        }
-        umma_commit(s_full(g, h & 1));
-      };
-      mbar_wait(q_full, 0);
-      if (max_sub > 0) {
-        need_tile(0);  // K_0
-        for (int h = 0; h < 2; ++h)
-          for (int g = 0; g < 2; ++g)
-            if (h < n_sub[g]) issue_s(g, h);
-        umma_commit(slot_empty(0));  // both halves of K_0 have been issued (S_0, S_1): release it once they retire
-      }
-      for (int h = 0; h < max_sub; ++h) {
-        for (int g = 0; g < 2; ++g) {
-          if (h >= n_sub[g]) continue;
-          mbar_wait(p_ready(g, h & 1), (h >> 1) & 1);  // softmax wrote P_h (and rescaled O if it had to)
-          tc_fence_after();
-          need_tile(2 * (h >> 1) + 1);                 // V of this 128-key tile
-          const uint32_t sV = smem_base + kSmemKV + ((2 * (h >> 1) + 1) % NSLOT) * kTileBytes + (h & 1) * (HN * 128);
-#pragma unroll
-          for (int ks = 0; ks < HN / 16; ++ks) {  // 16 keys = 8 packed P columns per step
-            const uint64_t bd = umma_desc_sw128(sV + ks * 2048, BN * 128, 1024);
-            umma_bf16_ts(tmem_base + g * 256 + 128, tmem_base + g * 256 + (h & 1) * HN + ks * 8, bd, idesc_o, (h | ks) != 0);
-          }
-          umma_commit(o_done(g));
-          if (h + 2 < n_sub[g]) {
-            need_tile(2 * ((h + 2) >> 1));  // K of the tile S_{h+2} reads
-            issue_s(g, h + 2);              // runs after PV_h in the pipe: the buffer it overwrites has been drained
-          }
-        }
-        // ring release: V tile h>>1 after its second half (or the very last sub-tile); K tile (h+2)>>1 likewise
-        if ((h & 1) == 1 || h == max_sub - 1) umma_commit(slot_empty((2 * (h >> 1) + 1) % NSLOT));
-        if (h + 2 < max_sub && (((h + 2) & 1) == 1 || h + 2 == max_sub - 1)) umma_commit(slot_empty((2 * ((h + 2) >> 1)) % NSLOT));
-      }
-    }
-  } else {
-    // ===== softmax warpgroups: one query row per thread, 64-key sub-tiles =====
-    const int g = warp >> 2;
-    const int t = threadIdx.x & 127;
-    const int n_my = n_sub[g];
-    const int row = qblk * 2 * BM + g * BM + t;
-    const int limit = shift + row;
-    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t tG = tmem_base + g * 256 + lane_off;  // S0 | S1 (64 fp32 columns each; P = first 32 packed columns)
-    const uint32_t tO = tG + 128;
-    constexpr float kRescaleThreshold = 8.0f;
-    auto exp2_poly2 = [](float x) {  // XU-free 2^x, x <= 0 (see the v4 kernel)
-      x = fmaxf(x, -126.f);
-      const float tt = x + 12582912.f;
-      const float f = x - (tt - 12582912.f);
-      float pfr = fmaf(f, 0.05517210811376572f, 0.24261118471622467f);
-      pfr = fmaf(pfr, f, 0.693260908126831f);
-      pfr = fmaf(pfr, f, 0.9999280571937561f);
-      return __int_as_float(__float_as_int(pfr) + (__float_as_int(tt) << 23));
-    };
-
-    float m_ref = -INFINITY, l_run = 0.f;
-    for (int h = 0; h < n_my; ++h) {
-      const int b = h & 1;
-      const uint32_t tS = tG + b * HN;
-      mbar_wait(s_full(g, b), (h >> 1) & 1);
-      tc_fence_after();
-      uint32_t sr[2][32];
-      tmem_ld_32x32b_x32(tS, sr[0]);
-      tmem_ld_32x32b_x32(tS + 32, sr[1]);
-      tmem_ld_wait();
-      const int kbase = h * HN;
-      if ((kbase + HN - 1 > limit) || (kbase + HN > Lk)) {
-#pragma unroll
-        for (int c = 0; c < HN; ++c)
-          if (kbase + c > limit || kbase + c >= Lk) sr[c >> 5][c & 31] = 0xff800000u;  // -inf
-      }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-      for (int c = 0; c < HN; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sr[c >> 5][c & 31]));
-      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      const bool refresh = (mx - m_ref) * p.scale_log2 > kRescaleThreshold;
-      float corr = 1.f;
-      if (refresh) {
-        corr = (m_ref == -INFINITY) ? 0.f : fast_exp2((m_ref - mx) * p.scale_log2);
-        m_ref = mx;
-        l_run *= corr;
-      }
-      // P_h against the (possibly refreshed) reference maximum: independent of O, so it is produced BEFORE synchronising
-      // with PV_{h-1}; it goes over S_h's own buffer, which no MMA in flight reads (PV_{h-1} reads the other buffer).
-      const float moff = (m_ref == -INFINITY) ? 0.f : m_ref * p.scale_log2;
-      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
-      uint32_t pk[32];
-#pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const int c = e * 2;
-        const float a0 = fmaf(__uint_as_float(sr[c >> 5][c & 31]), p.scale_log2, -moff);
-        const float a1 = fmaf(__uint_as_float(sr[(c + 1) >> 5][(c + 1) & 31]), p.scale_log2, -moff);
-        const float p0 = fast_exp2(a0);                                // MUFU
-        const float p1 = (e & 1) ? exp2_poly2(a1) : fast_exp2(a1);     // every 4th exponential on the FMA pipe
-        ls4[e & 3] += p0 + p1;
-        pk[e] = pack_bf16x2(p0, p1);
-      }
-      tmem_st_32x32b_x32(tS, pk);
-      l_run += (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-      // O is touched (rarely) only once PV_{h-1} has retired.  The wait is unconditional so that the o_done phases are
-      // consumed strictly in order (a parity wait may never lag two phases behind); by now PV_{h-1} has usually retired.
-      if (h > 0) {
-        mbar_wait(o_done(g), (h - 1) & 1);
-        tc_fence_after();
-        if (__any_sync(0xffffffffu, refresh)) {  // tcgen05.ld/st are warp-collective
-#pragma unroll
-          for (int c = 0; c < D / 32; ++c) {
-            uint32_t orr[32];
-            tmem_ld_32x32b_x32(tO + c * 32, orr);
-            tmem_ld_wait();
-#pragma unroll
-            for (int e = 0; e < 32; ++e) orr[e] = __float_as_uint(__uint_as_float(orr[e]) * corr);
-            tmem_st_32x32b_x32(tO + c * 32, orr);
-          }
-        }
-      }
-      tmem_st_wait();
-      tc_fence_before();
-      mbar_arrive(p_ready(g, b));
-    }
-    float acc[D];
-    if (n_my > 0) {
-      mbar_wait(o_done(g), (n_my - 1) & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t orr[32];
-        tmem_ld_32x32b_x32(tO + c * 32, orr);
-        tmem_ld_wait();
-#pragma unroll
-        for (int e = 0; e < 32; ++e) acc[c * 32 + e] = __uint_as_float(orr[e]);
-      }
-      tc_fence_before();
-    }
-    if (n_my > 0 && row < Lq) {
-      const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
-      bf16* orow = p.out + static_cast<int64_t>(q0 + row) * p.out_stride + head * D;
-#pragma unroll
-      for (int c = 0; c < D / 8; ++c) {
-        uint4 v;
-        v.x = pack_bf16x2(acc[c * 8 + 0] * inv, acc[c * 8 + 1] * inv);
-        v.y = pack_bf16x2(acc[c * 8 + 2] * inv, acc[c * 8 + 3] * inv);
-        v.z = pack_bf16x2(acc[c * 8 + 4] * inv, acc[c * 8 + 5] * inv);
-        v.w = pack_bf16x2(acc[c * 8 + 6] * inv, acc[c * 8 + 7] * inv);
-        *reinterpret_cast<uint4*>(orow + c * 8) = v;
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) {
-    tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
-  }
-}
-
 }  // namespace nvllm
 
 extern "C" int nvllm_varlen_prefill_attention(void* out, const void* q, const void* k, const void* v,
@@ -670,33 +390,24 @@ extern "C" int nvllm_varlen_prefill_attention(void* out, const void* q, const vo
   p.Hkv = num_kv_heads;
   p.out_stride = out_token_stride;
   p.scale_log2 = scale * 1.4426950408889634f;
-  static bool attr_set = false;
-  if (!attr_set) {
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
-    NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytes));
-    attr_set = true;
+  {
+    static std::once_flag once;
+    static cudaError_t once_err = cudaSuccess;
+    std::call_once(once, [] {
+      const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+      cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<1>, attr, pf::kSmemBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(prefill_attn_kernel<2>, attr, pf::kSmemBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(prefill_attn_kernel<3>, attr, pf::kSmemBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(prefill_attn_kernel<4>, attr, pf::kSmemBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(prefill_attn_kernel<5>, attr, pf::kSmemBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(prefill_attn_kernel<6>, attr, pf::kSmemBytes);
+      once_err = e;
+    });
+    NVLLM_CUDA(once_err);
   }
   (void)max_seqlen_k;
   dim3 grid((max_seqlen_q + 2 * pf::BM - 1) / (2 * pf::BM), num_heads, batch);
-  {
-    const char* v5 = getenv("NVLLM_PREFILL_V5");  // opt-in: 64-key sub-tiles with double-buffered S (unvalidated, see above)
-    if (v5 && v5[0] == '1') {
-      static bool v5_attr = false;
-      if (!v5_attr) {
-        NVLLM_CUDA(cudaFuncSetAttribute(prefill_attn_v5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, pf::kSmemBytesV5));
-        v5_attr = true;
-      }
-      NVLLM_CUDA(launch_pdl(prefill_attn_v5_kernel, grid, dim3(pf::kThreads), pf::kSmemBytesV5, static_cast<cudaStream_t>(stream),
-                            tq, tk, tv, p));
-      return 0;
-    }
-  }
-  const char* pe = getenv("NVLLM_PREFILL_POLY");
-  const int poly = pe ? atoi(pe) : 4;  // XU-free polynomial on 1/4 of the exponentials: +26 % at 4K, 1060 TFLOP/s at 32K
+  const int poly = knobs().prefill_poly;  // XU-free polynomial on 1/4 of the exponentials: +26 % at 4K, 1060 TFLOP/s at 32K
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (poly == 2) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<2>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));
   else if (poly == 3) NVLLM_CUDA(launch_pdl(prefill_attn_kernel<3>, grid, dim3(pf::kThreads), pf::kSmemBytes, st, tq, tk, tv, p));

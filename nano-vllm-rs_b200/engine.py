@@ -61,6 +61,7 @@ ENGINE_PROTOTYPES = {
     "nvllm_scheduler_block_info": (i32, [vp, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(u64)]),
     "nvllm_scheduler_free_list": (i32, [vp, vp, i32]),
     "nvllm_scheduler_sequence": (i32, [vp, i64, vp, i32, C.POINTER(i32), C.POINTER(i32)]),
+    "nvllm_scheduler_release_sequence": (i32, [vp, i64]),
     "nvllm_runner_create": (i32, [C.POINTER(vp), C.POINTER(CConfig), vp]),
     "nvllm_runner_destroy": (i32, [vp]),
     "nvllm_runner_init_weights": (i32, [vp, u64, f32]),
@@ -243,6 +244,11 @@ class Scheduler:
         lib().nvllm_scheduler_free_list(self.h, a.ctypes.data, n)
         return a[:n].tolist()
 
+    def release_sequence(self, seq_id):
+        """Frees a FINISHED sequence's storage (its outputs have been handed to the caller); sequence(seq_id) raises
+        KeyError afterwards."""
+        check(lib().nvllm_scheduler_release_sequence(self.h, seq_id))
+
     def sequence(self, seq_id):
         npt, st = i32(), i32()
         n = lib().nvllm_scheduler_sequence(self.h, seq_id, None, 0, C.byref(npt), C.byref(st))
@@ -388,6 +394,7 @@ class LLMEngine:
             if s["status"] == "Finished":
                 done.append(self._output(sid, s))
                 del self._live[sid]
+                self.scheduler.release_sequence(sid)   # handed to the caller: the engine forgets it (llm_engine.rs:186-193)
         return done
 
     def generate(self, prompts, sampling_params: SamplingParams = None):
@@ -400,6 +407,7 @@ class LLMEngine:
             s = self.scheduler.sequence(i)
             self._live.pop(i, None)
             out.append(s["token_ids"][s["num_prompt_tokens"]:])
+            self.scheduler.release_sequence(i)
         return out
 
     def generate_outputs(self, prompts, sampling_params: SamplingParams = None) -> List[SequenceOutput]:
@@ -407,9 +415,12 @@ class LLMEngine:
         ids = [self.add_request(p, sampling_params) for p in prompts]
         while not self.is_finished():
             self.step()
+        outs = []
         for i in ids:
             self._live.pop(i, None)
-        return [self._output(i, self.scheduler.sequence(i)) for i in ids]
+            outs.append(self._output(i, self.scheduler.sequence(i)))
+            self.scheduler.release_sequence(i)
+        return outs
 
     def generate_stream(self, prompts, sampling_params: SamplingParams = None):
         """LLMEngine::generate_stream (llm_engine.rs:101-128) as a generator: after every step yields one SequenceOutput per
@@ -427,6 +438,7 @@ class LLMEngine:
                 if s["status"] == "Finished":
                     del seen[i]
                     self._live.pop(i, None)
+                    self.scheduler.release_sequence(i)
 
     def get_stats(self):
         """EngineStats (llm_engine.rs:312-327,375-400): scheduler counters + block-memory utilisation (percent)."""

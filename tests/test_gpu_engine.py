@@ -216,8 +216,6 @@ def test_engine_facade_stream_outputs_stats(cuda):
         E.LLMEngine(cfg, std=0.05).add_request("needs a tokenizer")
 
 
-@pytest.mark.xfail(strict=False, reason="added after the round's GPU budget was spent: first GPU run pending (an XPASS is the "
-                                        "expected outcome; every link of the chain is validated separately)")
 def test_gpu_engine_vs_hf_transformers_golden(cuda):
     """The GPU engine against an INDEPENDENT implementation directly: weights of tests/golden/qwen3_hf.json (non-unit norm
     weights) loaded through nvllm_runner_load_weight, prefill + three teacher-forced decode steps, logits vs Hugging Face

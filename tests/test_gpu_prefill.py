@@ -94,12 +94,3 @@ def test_varlen_prefill_full_size_vs_torch(cuda):
         vv = v[sl].float().permute(1, 0, 2).repeat_interleave(H // Hkv, 0)
         ref = torch.nn.functional.scaled_dot_product_attention(qq, kk, vv, is_causal=True).permute(1, 0, 2)
         assert_close(to_np_f32(out[sl]), to_np_f32(ref), ATT_ATOL, ATT_RTOL, f"prefill full-size seq {b}")
-
-
-@pytest.mark.skipif(os.environ.get("NVLLM_TEST_V5") != "1",
-                    reason="opt-in: the v5 prefill kernel (64-key sub-tiles, double-buffered S) was written without GPU time "
-                           "left in round 1; run with NVLLM_TEST_V5=1 to validate it before making it the default")
-@pytest.mark.parametrize("lens,H,Hkv", DENSE, ids=[str(i) for i in range(len(DENSE))])
-def test_varlen_prefill_v5_dense_vs_oracle(cuda, lens, H, Hkv, monkeypatch):
-    monkeypatch.setenv("NVLLM_PREFILL_V5", "1")
-    test_varlen_prefill_dense_vs_oracle(cuda, lens, H, Hkv)

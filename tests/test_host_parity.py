@@ -222,3 +222,75 @@ def test_cfg4_full_size_shared_prefix_trace_appendix_b():
     assert sc.get_stats()["used_blocks"] == 272 + 256
     sc.postprocess(np.zeros(B, np.int64))
     assert sc.is_finished() and sc.get_stats()["used_blocks"] == 0
+
+
+def test_max_model_len_is_enforced_at_admission():
+    """nothing bounded prompt + max_tokens by max_model_len (the reference carries the field, config.rs:27,60, and
+    never reads it): a sequence could outgrow the runner's block tables mid-run.  Now the prompt is refused (no state
+    change) when it cannot fit, and max_tokens is clamped so the sequence ends with len == max_model_len + 1 at the latest —
+    in lockstep with the oracle scheduler given the clamped max_tokens explicitly."""
+    bs, mml = 16, 64
+    cfg = E.Config("tiny", kvcache_block_size=bs, num_kvcache_blocks=32, max_model_len=mml, max_num_batched_tokens=256)
+    sc = E.Scheduler(cfg)
+    with pytest.raises(E._ffi.NvllmError) as ei:
+        sc.add_sequence(list(range(mml + 1)), E.SamplingParams(temperature=0.0, max_tokens=4))
+    assert ei.value.code == -1 and sc.get_stats()["total_sequences"] == 0 and sc.is_finished()
+    with pytest.raises(E._ffi.NvllmError):
+        E.Scheduler(E.Config("tiny", kvcache_block_size=bs, num_kvcache_blocks=32, max_model_len=4096,
+                             max_num_batched_tokens=128)).add_sequence(list(range(129)), E.SamplingParams(max_tokens=1))
+    # prompt of 60 tokens, max_tokens 64 -> clamped to 64 - 60 + 1 = 5 completions; the longest context ever scheduled is 64
+    prompts = [list(range(60)), list(range(100, 164)), list(range(7))]
+    asked = [64, 64, 200]
+    clamped = [5, 1, 58]
+    ids = [sc.add_sequence(p, E.SamplingParams(temperature=0.0, max_tokens=m, ignore_eos=True)) for p, m in zip(prompts, asked)]
+    osc = H.Scheduler(H.Config(kvcache_block_size=bs, num_kvcache_blocks=32, max_num_batched_tokens=256))
+    oseqs = [H.Sequence(p, H.SamplingParams(temperature=0.0, max_tokens=m, ignore_eos=True), block_size=bs)
+             for p, m in zip(prompts, clamped)]
+    for s in oseqs:
+        osc.add_sequence(s)
+    longest = 0
+    while not osc.is_finished():
+        batch, is_prefill = osc.schedule()
+        o = H.prepare_prefill(batch, bs) if is_prefill else H.prepare_decode(batch, bs)
+        c = sc.schedule()
+        assert c.is_prefill == is_prefill
+        _eq(c.slot_mapping, o.slot_mapping, "slot_mapping"); _eq(c.block_tables, o.block_tables, "block_tables")
+        if not is_prefill:
+            longest = max(longest, int(c.context_lens.max()))
+            assert c.block_tables.shape[1] <= mml // bs
+        toks = [3] * len(batch)
+        osc.postprocess(batch, toks); sc.postprocess(toks)
+    assert sc.is_finished() and longest == mml
+    assert [len(sc.sequence(i)["token_ids"]) - len(p) for i, p in zip(ids, prompts)] == clamped
+
+
+def test_release_sequence_recycles_the_slab_and_never_reuses_ids():
+    sc = E.Scheduler(E.Config("tiny", kvcache_block_size=16, num_kvcache_blocks=32))
+    a = sc.add_sequence([1, 2, 3], E.SamplingParams(temperature=0.0, max_tokens=1))
+    b = sc.add_sequence([4, 5], E.SamplingParams(temperature=0.0, max_tokens=3))
+    with pytest.raises(E._ffi.NvllmError):
+        sc.release_sequence(a)                    # still waiting
+    sc.schedule(); sc.postprocess([9, 9])          # prefill: a finishes (max_tokens 1)
+    assert sc.sequence(a)["status"] == "Finished" and sc.sequence(b)["status"] == "Running"
+    sc.release_sequence(a)
+    with pytest.raises(KeyError):
+        sc.sequence(a)
+    with pytest.raises(E._ffi.NvllmError):
+        sc.release_sequence(a)
+    c = sc.add_sequence([6, 7, 8, 9], E.SamplingParams(temperature=0.0, max_tokens=2))   # takes a's slab slot, a NEW id
+    assert c == 2 and sc.sequence(c)["token_ids"] == [6, 7, 8, 9] and sc.sequence(b)["token_ids"] == [4, 5, 9]
+    while not sc.is_finished():
+        bt = sc.schedule()
+        sc.postprocess([1] * len(bt.seq_ids))
+    assert sc.sequence(b)["token_ids"] == [4, 5, 9, 1, 1] and sc.sequence(c)["token_ids"] == [6, 7, 8, 9, 1, 1]
+    assert sc.get_stats()["used_blocks"] == 0 and sc.get_stats()["finished"] == 3
+
+
+def test_config_validate_mirrors_the_kernel_constraints():
+    for bs in (48, 80, 192):          # % 16 == 0 but neither a divisor nor a multiple of the prefill kernel's 128-key tile
+        with pytest.raises(Exception):
+            E.Config("tiny", kvcache_block_size=bs).validate()
+    for bs in (16, 32, 64, 128, 256, 512):
+        E.Config("tiny", kvcache_block_size=bs).validate()
+    with pytest.raises(Exception):
+        E.Config("tiny", head_dim=64).validate()
