@@ -250,6 +250,11 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base);
 int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
                                 int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream);
 
+/* 0, or NVLLM_ERR_COMM once a fused kernel of this communicator gave up waiting for a peer (a rank died, or stalled for
+ * longer than NVLLM_COMM_TIMEOUT_MS, default 10 min).  The kernel neither hangs nor traps: it raises this host-visible
+ * flag, stops waiting in later calls and runs to completion; results from then on are undefined.  Sticky. */
+int nvllm_comm_error(const nvllm_comm* comm);
+
 /* Deterministic seeded weight init shared bit-for-bit with the CPU oracle (oracle/weights.py):
  * element i of tensor `tensor_id` = bf16( (sum of the four 16-bit fields of
  * splitmix64(seed ^ tensor_id<<40, i)  - 131070) * std_scale ).  Integer arithmetic + one exact

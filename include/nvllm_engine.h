@@ -138,6 +138,14 @@ int nvllm_runner_execute(nvllm_runner* r, const nvllm_batch* batch, int64_t* h_t
 int nvllm_runner_execute_async(nvllm_runner* r, const nvllm_batch* batch);
 int nvllm_runner_fetch_tokens(nvllm_runner* r, int64_t* h_tokens, int32_t n);
 void* nvllm_runner_stream(nvllm_runner* r);
+/* Per-launch profile of EAGER steps (enforce_eager, prefill, or the first use of a decode bucket): while enabled the
+ * runner records a CUDA event after every launch; consecutive differences are serialised per-kernel times (an event
+ * between two launches also removes their programmatic overlap).  This is the launch list for multi-rank runs, where
+ * kernels that wait for peers cannot be serialised by ncu.  enable = 1 clears the accumulators and starts, 0 stops.
+ * nvllm_runner_profile_report writes "name\tlaunches\ttotal_us\n" lines into h_buf (NUL-terminated, truncated to cap) and
+ * returns the full length. */
+int nvllm_runner_profile(nvllm_runner* r, int32_t enable);
+int64_t nvllm_runner_profile_report(nvllm_runner* r, char* h_buf, size_t cap);
 /* Number of kernels launched by the last execute (decode graph node count, or eager launches). */
 int64_t nvllm_runner_last_launches(const nvllm_runner* r);
 /* Device pointers of layer `layer`'s K / V cache and the layout in use (tests). */

@@ -65,14 +65,16 @@ static int nccl_status(int rc, const char* what) {
 
 }  // namespace nvllm
 
-// Symmetric region: [control block 4 KiB | user data].  Control block (all uint32, written remotely by peers):
-//   ready[8] at +0, done[8] at +256, then local-only: counter at +512, epoch at +516.
+// Symmetric region: [control block 4 KiB | user data].  Control block (all uint32; the first two arrays are written
+// remotely by peers):  ready[8] at +0, done[8] at +256, then local-only: CTA counter at +512, epoch at +516, dead at +520.
 struct nvllm_comm {
   nvllm::ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
   uint8_t* sym_local = nullptr;       // this rank's region (cudaMalloc)
   uint8_t* sym_peer[8] = {nullptr};   // every rank's region as mapped into this process (own entry == sym_local)
   size_t sym_bytes = 0;
+  int* h_err = nullptr;               // pinned + mapped: a fused kernel that gave up waiting for a peer sets it
+  int* d_err = nullptr;               // device alias of h_err
 };
 
 namespace nvllm {
@@ -86,80 +88,125 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t target) {
+// 16-byte COHERENT load of data another GPU wrote while this kernel may already be running (ordered after the flag
+// acquire): never through the non-coherent path, never from L1 — ld.global.nc is outside the PTX memory model for
+// memory that changes during the kernel's lifetime.
+__device__ __forceinline__ uint4 ld_sys_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+// Spins until *p reaches `target` (wrap-safe).  A peer that never arrives (crashed rank, a host-side stall longer than
+// NVLLM_COMM_TIMEOUT_MS) must neither hang the GPU nor poison the CUDA context: the kernel raises the host-visible error
+// flag, marks the communicator dead (later calls stop waiting) and runs to completion; the host reports NVLLM_ERR_COMM.
+__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t target, long long timeout_cycles, uint32_t* dead,
+                                          int* err) {
+  if (static_cast<int32_t>(ld_acquire_sys(p) - target) >= 0) return;
   const long long t0 = clock64();
   while (static_cast<int32_t>(ld_acquire_sys(p) - target) < 0) {
-    if (clock64() - t0 > 8000000000ll) {  // a peer never arrived: fail loudly instead of hanging the GPU
-      printf("nvllm: peer flag timeout (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
+    if (clock64() - t0 > timeout_cycles) {
+      *reinterpret_cast<volatile uint32_t*>(dead) = 1u;
+      *reinterpret_cast<volatile int*>(err) = 1;
+      __threadfence_system();
+      return;
     }
   }
 }
 
 struct FusedArParams {
   uint8_t* peer[8];          // symmetric regions of all ranks as mapped here
+  uint8_t* self;             // == peer[rank] (kept apart: a run-time index into peer[] would spill the parameter block)
   size_t x_off, res_off, out_off;  // byte offsets of the partial sums / residual / normed buffers inside a region
   const bf16* weight;
-  int rank, world, num_tokens, hidden;
+  int rank, num_tokens, hidden;
   float eps;
+  long long timeout_cycles;
+  int* err;
 };
 
 // Two-shot all-reduce fused with the residual add and the RMSNorm that always follow it (qwen3.rs:382-385,389):
-//   shot 1  rank r owns rows [r*R, (r+1)*R): it reads those rows of every rank's partial sums over NVLink (16-byte
-//           peer loads, fixed rank order -> bit-identical on every rank), rounds the sum to bf16 (the all-reduced tensor),
-//           adds the residual (bf16 tensor add), normalises in f32;
+//   shot 1  rank r owns rows [r*R, (r+1)*R): it reads those rows of every rank's partial sums over NVLink — WORLD is a
+//           template parameter and a thread's WORLD x min(VPT, 2) 16-byte peer loads are all issued before the first add,
+//           so one CTA keeps up to 64 KiB in flight per row (the round-1 kernel issued its peer loads one behind the other
+//           through a run-time loop: ~8x less memory-level parallelism on a ~2 us NVLink round trip).  Fixed rank order of
+//           the adds -> bit-identical on every rank.  The sum is rounded to bf16 (the all-reduced tensor), the residual
+//           added (bf16 tensor add), the row normalised in f32;
 //   shot 2  it writes the normed rows into EVERY rank's buffer (peer stores); the new residual rows stay on the owner
 //           (the residual stream is row-sharded across ranks between the fused kernels of one forward).
 // Flags in the control block: `ready` (my partial sums are complete / my buffers may be overwritten) before shot 1,
 // `done` (all my remote writes are visible) before the kernel may complete.  Epoch counters live in device memory and
 // advance inside the kernel, so a captured CUDA graph can replay it.
-__global__ void __launch_bounds__(1024)
+// p.peer[q] for a run-time q without indexing the parameter array dynamically (which would copy it to local memory).
+__device__ __forceinline__ uint8_t* peer_of(const FusedArParams& p, unsigned q) {
+  uint8_t* r = p.peer[0];
+#pragma unroll
+  for (unsigned i = 1; i < 8; ++i) r = (q == i) ? p.peer[i] : r;
+  return r;
+}
+
+template <int WORLD, int VPT>
+__global__ void __launch_bounds__(512)
 allreduce_add_rmsnorm_kernel(const FusedArParams p) {
   pdl_launch_dependents();
   pdl_wait();
-  uint32_t* ctrl = reinterpret_cast<uint32_t*>(p.peer[p.rank]);
+  uint32_t* ctrl = reinterpret_cast<uint32_t*>(p.self);
   const uint32_t epoch = ctrl[129] + 1;  // +516 bytes; written only by this rank's last CTA of the previous call
-  if (blockIdx.x == 0 && threadIdx.x < p.world) {
+  const bool dead = ctrl[130] != 0;      // a previous call timed out: never wait again (the host reports the error)
+  if (blockIdx.x == 0 && threadIdx.x < WORLD) {
     __threadfence_system();
-    st_release_sys(reinterpret_cast<uint32_t*>(p.peer[threadIdx.x]) + p.rank, epoch);  // ready[rank] on peer
+    st_release_sys(reinterpret_cast<uint32_t*>(peer_of(p, threadIdx.x)) + p.rank, epoch);  // ready[rank] on peer
   }
-  if (threadIdx.x < p.world) wait_flag(ctrl + threadIdx.x, epoch);  // everybody's partial sums are complete
-  __syncthreads();
+  if (threadIdx.x < WORLD && !dead) wait_flag(ctrl + threadIdx.x, epoch, p.timeout_cycles, ctrl + 130, p.err);
+  __syncthreads();  // everybody's partial sums are complete (and ordered before the loads below: acquire + barrier)
 
-  const int rows_per = (p.num_tokens + p.world - 1) / p.world;
+  const int rows_per = (p.num_tokens + WORLD - 1) / WORLD;
   const int row0 = p.rank * rows_per;
   const int row1 = min(p.num_tokens, row0 + rows_per);
   const int nvec = p.hidden >> 3;
   const uint4* wv = reinterpret_cast<const uint4*>(p.weight);
-  __shared__ float red[32];
+  constexpr int KCH = VPT < 2 ? VPT : 2;  // vectors per thread whose peer loads are in flight together
+  __shared__ float red[16];
   __shared__ float s_inv;
   for (int row = row0 + blockIdx.x; row < row1; row += gridDim.x) {
     const size_t roff = static_cast<size_t>(row) * p.hidden * 2;
-    float v[2][8];
-    uint32_t sw[2][4];
+    uint32_t sw[VPT][4];  // the new residual row (packed bf16), kept for the second pass
     float ss = 0.f;
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-      const int i = threadIdx.x + k * blockDim.x;
-      if (i < nvec) {
-        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        for (int q = 0; q < p.world; ++q) {  // fixed order: identical bits on every rank
-          const uint4 a = ld_nc_16(p.peer[q] + p.x_off + roff + i * 16);
-          const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+    for (int k0 = 0; k0 < VPT; k0 += KCH) {
+      uint4 a[KCH][WORLD], r[KCH];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(aw[j]); acc[2 * j + 1] += bf16_hi(aw[j]); }
+      for (int k = 0; k < KCH; ++k) {
+        const int i = threadIdx.x + (k0 + k) * blockDim.x;
+        if (i < nvec) {
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q) a[k][q] = ld_sys_16(p.peer[q] + p.x_off + roff + i * 16);
+          r[k] = *reinterpret_cast<const uint4*>(p.self + p.res_off + roff + i * 16);
         }
-        const uint4 r = *reinterpret_cast<const uint4*>(p.peer[p.rank] + p.res_off + roff + i * 16);
-        const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+      }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint32_t o = pack_bf16x2(acc[2 * j], acc[2 * j + 1]);                        // the all-reduced bf16 tensor
-          sw[k][j] = pack_bf16x2(bf16_lo(o) + bf16_lo(rw[j]), bf16_hi(o) + bf16_hi(rw[j]));  // + residual (bf16 add)
-          v[k][2 * j] = bf16_lo(sw[k][j]);
-          v[k][2 * j + 1] = bf16_hi(sw[k][j]);
+      for (int k = 0; k < KCH; ++k) {
+        const int i = threadIdx.x + (k0 + k) * blockDim.x;
+        if (i < nvec) {
+          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q) {  // fixed order: identical bits whichever rank owns the row
+            const uint32_t aw[4] = {a[k][q].x, a[k][q].y, a[k][q].z, a[k][q].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(aw[j]); acc[2 * j + 1] += bf16_hi(aw[j]); }
+          }
+          const uint32_t rw[4] = {r[k].x, r[k].y, r[k].z, r[k].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t o = pack_bf16x2(acc[2 * j], acc[2 * j + 1]);                          // the all-reduced bf16 tensor
+            const uint32_t h = pack_bf16x2(bf16_lo(o) + bf16_lo(rw[j]), bf16_hi(o) + bf16_hi(rw[j]));  // + residual (bf16 add)
+            sw[k0 + k][j] = h;
+            const float v0 = bf16_lo(h), v1 = bf16_hi(h);
+            ss += v0 * v0 + v1 * v1;
+          }
         }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) ss += v[k][j] * v[k][j];
       }
     }
     ss = warp_sum(ss);
@@ -173,7 +220,7 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
     __syncthreads();
     const float inv = s_inv;
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
+    for (int k = 0; k < VPT; ++k) {
       const int i = threadIdx.x + k * blockDim.x;
       if (i < nvec) {
         const uint4 w = __ldg(wv + i);
@@ -182,11 +229,12 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
         uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          ow[j] = pack_bf16x2(v[k][2 * j] * inv * bf16_lo(ww[j]), v[k][2 * j + 1] * inv * bf16_hi(ww[j]));
+          ow[j] = pack_bf16x2(bf16_lo(sw[k][j]) * inv * bf16_lo(ww[j]), bf16_hi(sw[k][j]) * inv * bf16_hi(ww[j]));
         // The residual stream stays ROW-SHARDED: its only readers are these fused kernels, and row `row` is always
         // reduced by this rank, so the new residual is written locally only (halves the NVLink write traffic).
-        *reinterpret_cast<uint4*>(p.peer[p.rank] + p.res_off + roff + i * 16) = make_uint4(sw[k][0], sw[k][1], sw[k][2], sw[k][3]);
-        for (int q = 0; q < p.world; ++q)  // shot 2: broadcast the normed row to every rank
+        *reinterpret_cast<uint4*>(p.self + p.res_off + roff + i * 16) = make_uint4(sw[k][0], sw[k][1], sw[k][2], sw[k][3]);
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)  // shot 2: broadcast the normed row to every rank
           *reinterpret_cast<uint4*>(p.peer[q] + p.out_off + roff + i * 16) = o;
       }
     }
@@ -199,9 +247,9 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
   if (threadIdx.x == 0) s_last = (atomicAdd(ctrl + 128, 1u) == gridDim.x - 1) ? 1u : 0u;
   __syncthreads();
   if (s_last) {
-    if (threadIdx.x < p.world) {
-      st_release_sys(reinterpret_cast<uint32_t*>(p.peer[threadIdx.x]) + 64 + p.rank, epoch);  // done[rank] on peer
-      wait_flag(ctrl + 64 + threadIdx.x, epoch);
+    if (threadIdx.x < WORLD) {
+      st_release_sys(reinterpret_cast<uint32_t*>(peer_of(p, threadIdx.x)) + 64 + p.rank, epoch);  // done[rank] on peer
+      if (!dead) wait_flag(ctrl + 64 + threadIdx.x, epoch, p.timeout_cycles, ctrl + 130, p.err);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -210,6 +258,20 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
       __threadfence();
     }
   }
+}
+
+template <int WORLD>
+static int launch_fused_ar(const FusedArParams& p, int rows_per, cudaStream_t st) {
+  const int nvec = p.hidden / 8;
+  const int vpt = nvec <= 128 ? 1 : (nvec <= 1024 ? 2 : 4);
+  int threads = ((nvec + vpt - 1) / vpt + 31) / 32 * 32;
+  if (threads < 32) threads = 32;
+  int grid = rows_per < 4 * sm_count() ? rows_per : 4 * sm_count();
+  if (grid < 1) grid = 1;
+  if (vpt == 1) NVLLM_CUDA(launch_pdl(allreduce_add_rmsnorm_kernel<WORLD, 1>, dim3(grid), dim3(threads), 0, st, p));
+  else if (vpt == 2) NVLLM_CUDA(launch_pdl(allreduce_add_rmsnorm_kernel<WORLD, 2>, dim3(grid), dim3(threads), 0, st, p));
+  else NVLLM_CUDA(launch_pdl(allreduce_add_rmsnorm_kernel<WORLD, 4>, dim3(grid), dim3(threads), 0, st, p));
+  return 0;
 }
 }  // namespace nvllm
 
@@ -279,6 +341,11 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base) {
     }
     comm->sym_peer[r] = static_cast<uint8_t*>(pp);
   }
+  if (comm->h_err == nullptr) {
+    NVLLM_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&comm->h_err), sizeof(int), cudaHostAllocMapped));
+    *comm->h_err = 0;
+    NVLLM_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&comm->d_err), comm->h_err, 0));
+  }
   comm->sym_local = static_cast<uint8_t*>(base);
   comm->sym_bytes = total;
   *local_base = comm->sym_local + kSymCtrlBytes;
@@ -303,16 +370,27 @@ int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* resi
                   "allreduce_add_rmsnorm: out / x / residual must be 16-byte aligned buffers inside the symmetric region");
   for (int r = 0; r < 8; ++r) p.peer[r] = r < comm->world ? comm->sym_peer[r] : nullptr;
   p.weight = static_cast<const bf16*>(weight);
-  p.rank = comm->rank; p.world = comm->world; p.num_tokens = num_tokens; p.hidden = hidden; p.eps = eps;
-  const int nvec = hidden / 8;
-  int threads = nvec <= 256 ? (nvec + 31) / 32 * 32 : ((nvec + 1) / 2 + 31) / 32 * 32;
-  if (threads > 1024) threads = 1024;
-  if (threads < 32 * ((comm->world + 31) / 32)) threads = 32;
+  p.self = comm->sym_local;
+  p.rank = comm->rank; p.num_tokens = num_tokens; p.hidden = hidden; p.eps = eps;
+  p.timeout_cycles = knobs().comm_timeout_ms * 2000000ll;  // clock64 ticks at <= 2 GHz
+  p.err = comm->d_err;
   const int rows_per = (num_tokens + comm->world - 1) / comm->world;
-  int grid = rows_per < 2 * sm_count() ? rows_per : 2 * sm_count();
-  if (grid < 1) grid = 1;
-  NVLLM_CUDA(launch_pdl(allreduce_add_rmsnorm_kernel, dim3(grid), dim3(threads), 0, static_cast<cudaStream_t>(stream), p));
-  return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (comm->world) {
+    case 2: return launch_fused_ar<2>(p, rows_per, st);
+    case 4: return launch_fused_ar<4>(p, rows_per, st);
+    case 8: return launch_fused_ar<8>(p, rows_per, st);
+    default: break;
+  }
+  NVLLM_CHECK_ARG(false, NVLLM_ERR_ARG, "allreduce_add_rmsnorm: world %d (2, 4 or 8)", comm->world);
+}
+
+// 0, or NVLLM_ERR_COMM once a fused kernel of this communicator has given up waiting for a peer (sticky).
+int nvllm_comm_error(const nvllm_comm* comm) {
+  if (comm == nullptr || comm->h_err == nullptr) return 0;
+  if (*reinterpret_cast<volatile int*>(comm->h_err) == 0) return 0;
+  nvllm::set_error("fused TP kernel: a peer rank did not arrive within NVLLM_COMM_TIMEOUT_MS (communicator is dead)");
+  return NVLLM_ERR_COMM;
 }
 
 int nvllm_comm_destroy(nvllm_comm* comm) {
@@ -331,6 +409,7 @@ int nvllm_comm_destroy(nvllm_comm* comm) {
     }
   }
   if (comm->sym_local) cudaFree(comm->sym_local);
+  if (comm->h_err) cudaFreeHost(comm->h_err);
   if (comm->comm && nvllm::nccl().ok) nvllm::nccl().CommDestroy(comm->comm);
   delete comm;
   return 0;

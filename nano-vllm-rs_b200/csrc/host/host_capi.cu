@@ -52,6 +52,10 @@ int nvllm_config_init(nvllm_config* c, const char* arch) {
     c->vocab_size = 1024; c->hidden_size = 256; c->intermediate_size = 512; c->num_hidden_layers = 2;
     c->num_attention_heads = 4; c->num_key_value_heads = 2; c->max_position_embeddings = 4096;
     c->tie_word_embeddings = 0;
+  } else if (!strcmp(arch, "qwen3-0.6b-2l")) {  // two layers at the real Qwen3-0.6B widths (HF golden fixture), small vocab
+    c->vocab_size = 2048; c->hidden_size = 1024; c->intermediate_size = 3072; c->num_hidden_layers = 2;
+    c->num_attention_heads = 16; c->num_key_value_heads = 8; c->max_position_embeddings = 4096;
+    c->tie_word_embeddings = 0;
   } else if (!strcmp(arch, "tiny-tp8")) {  // 2-layer test model whose head counts divide by 8
     c->vocab_size = 2048; c->hidden_size = 512; c->intermediate_size = 1024; c->num_hidden_layers = 2;
     c->num_attention_heads = 16; c->num_key_value_heads = 8; c->max_position_embeddings = 4096;

@@ -112,6 +112,13 @@ struct nvllm_runner {
   // load_weight bookkeeping: every tensor the architecture needs must have arrived before the first execute
   // (a partially loaded checkpoint would otherwise run on uninitialised layer weights)
   std::vector<uint32_t> loaded;  // per layer: bit mask of the 11 per-layer tensors; last entry: embed | lm_head | norm
+  // per-launch profile (nvllm_runner_profile): eager steps record a CUDA event after every launch; an event between two
+  // launches also breaks their programmatic overlap, so the differences are serialised per-kernel times — the
+  // multi-rank-safe counterpart of an ncu launch list (kernels that wait for peers cannot run under ncu's serialisation)
+  bool profiling = false;
+  std::vector<std::pair<const char*, cudaEvent_t>> prof_marks;
+  std::vector<cudaEvent_t> prof_pool;
+  std::map<std::string, std::pair<double, int64_t>> prof_acc;  // name -> (total us, launches)
   bool fuse_rope = false; // NVLLM_FUSE_ROPE=1: qkv GEMM epilogue does q/k norm + RoPE + KV store for decode-sized batches
   bool fused_tp = false;  // h / normed / proj live in NVLink-mapped symmetric memory; all-reduce fused with add + RMSNorm
 
@@ -119,6 +126,8 @@ struct nvllm_runner {
     for (auto& g : graphs)
       if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
     for (void* p : allocs) cudaFree(p);
+    for (auto& m : prof_marks) cudaEventDestroy(m.second);
+    for (cudaEvent_t e : prof_pool) cudaEventDestroy(e);
     if (h_meta) cudaFreeHost(h_meta);
     if (h_tokens) cudaFreeHost(h_tokens);
     if (h_samp) cudaFreeHost(h_samp);
@@ -147,6 +156,27 @@ struct nvllm_runner {
   int execute_async(const nvllm_batch& b);
   int fetch(int64_t* out, int n);
   int sample(const nvllm_batch& b);
+  void mark(const char* name) {  // after a launch: no-op unless profiling an eager (non-captured) step
+    if (!profiling) return;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return;
+    cudaEvent_t e = nullptr;
+    if (!prof_pool.empty()) { e = prof_pool.back(); prof_pool.pop_back(); }
+    else if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, stream);
+    prof_marks.emplace_back(name, e);
+  }
+  void prof_collect() {  // stream must be idle
+    for (size_t i = 1; i < prof_marks.size(); ++i) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, prof_marks[i - 1].second, prof_marks[i].second) == cudaSuccess) {
+        auto& a = prof_acc[prof_marks[i].first];
+        a.first += ms * 1e3; a.second += 1;
+      }
+    }
+    for (auto& m : prof_marks) prof_pool.push_back(m.second);
+    prof_marks.clear();
+  }
 };
 
 // ------------------------------------------------------------------------------------------------ create
@@ -427,29 +457,36 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
   const float scale = 1.0f / sqrtf(static_cast<float>(D));  // attention.rs:45
   const int HD = H * D;
   launches = 0;
-  auto gemm = [&](void* y, const void* x, const void* w, int n, int k, int64_t ldy, int out_dt) {
+  mark("(step start)");
+  auto gemm = [&](void* y, const void* x, const void* w, int n, int k, int64_t ldy, int out_dt, const char* what) {
     ++launches;
-    return nvllm_gemm_bf16(y, x, w, N, n, k, k, k, ldy, out_dt, nullptr, 0, st);
+    const int rc = nvllm_gemm_bf16(y, x, w, N, n, k, k, k, ldy, out_dt, nullptr, 0, st);
+    mark(what);
+    return rc;
   };
   // h += all-reduce(proj); normed = rmsnorm(h) * w — the reference's RowParallelLinear all-reduce TODO (linear.rs:236)
   // followed by the residual add + norm: one fused kernel over NVLink peer memory, or NCCL + add_rmsnorm.
   auto add_norm = [&](const bf16* w) -> int {
     if (tp > 1 && fused_tp) {
       ++launches;
-      return nvllm_allreduce_add_rmsnorm(comm, normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+      const int rc = nvllm_allreduce_add_rmsnorm(comm, normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+      mark("allreduce_add_rmsnorm (fused TP epilogue)");
+      return rc;
     }
-    if (tp > 1) { RUN(nvllm_allreduce(comm, proj, static_cast<size_t>(N) * hidden, NVLLM_BF16, st)); ++launches; }
+    if (tp > 1) { RUN(nvllm_allreduce(comm, proj, static_cast<size_t>(N) * hidden, NVLLM_BF16, st)); ++launches; mark("ncclAllReduce"); }
     ++launches;
-    return nvllm_add_rmsnorm(normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+    const int rc = nvllm_add_rmsnorm(normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+    mark("add_rmsnorm");
+    return rc;
   };
-  RUN(nvllm_embedding_gather(h, embed, d_ids, N, hidden, vocab, NVLLM_BF16, st)); ++launches;
+  RUN(nvllm_embedding_gather(h, embed, d_ids, N, hidden, vocab, NVLLM_BF16, st)); ++launches; mark("embedding_gather");
   const int splits = is_prefill ? 1 : nvllm_paged_decode_choose_splits(N, H, Hkv, table_cap * layout.block_size);
   if (!is_prefill) last_decode_splits = splits;
   for (int l = 0; l < layers; ++l) {
     const LayerWeights& w = lw[l];
     // input_layernorm; for l > 0 fused with the residual add of the previous MLP output (qwen3.rs:389 -> :378)
     // (and, under TP, with the all-reduce of that output: see add_norm below)
-    if (l == 0) { RUN(nvllm_add_rmsnorm(normed, h, nullptr, w.input_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches; }
+    if (l == 0) { RUN(nvllm_add_rmsnorm(normed, h, nullptr, w.input_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches; mark("add_rmsnorm"); }
     else RUN(add_norm(w.input_ln));
     if (fuse_rope && D == 128 && N <= 256) {
       // decode-sized batches: qkv GEMM with q/k norm + RoPE + KV-cache store in its epilogue (one head per 128-wide tile)
@@ -457,48 +494,55 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
       RUN(nvllm_gemm_qkv_rope_store(qkv, normed, w.qkv, N, hidden, hidden, hidden, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr,
                                     cfg.qk_norm ? w.k_norm : nullptr, eps, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l],
                                     d_slots, &layout, st));
+      mark("qkv_proj GEMM + rope/store epilogue");
     } else {
-      RUN(gemm(qkv, normed, w.qkv, qkv_dim, hidden, qkv_dim, NVLLM_BF16));
+      RUN(gemm(qkv, normed, w.qkv, qkv_dim, hidden, qkv_dim, NVLLM_BF16, "qkv_proj GEMM"));
       // q/k norm + RoPE in place, K/V of this step into the cache (store before attention: note N2)
       RUN(nvllm_qknorm_rope_store(qkv, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr, cfg.qk_norm ? w.k_norm : nullptr, eps,
                                   N, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l], d_slots, &layout, NVLLM_BF16, st)); ++launches;
+      mark("qknorm_rope_store");
     }
     if (!is_prefill) {
       RUN(nvllm_paged_decode_attention(attn, qkv, kc[l], vc[l], d_tables, d_ctx, N, H, table_cap, qkv_dim, HD, &layout,
                                        scale, decode_ws, decode_ws_bytes, splits, NVLLM_BF16, st));
       launches += splits > 1 ? 2 : 1;
+      mark("paged_decode_attention");
     } else {
       RUN(nvllm_varlen_prefill_attention(attn, qkv, qkv + HD, qkv + HD + Hkv * D, d_cu_q, d_cu_k, S, N, N, b.max_seqlen_q,
                                          b.max_seqlen_k, H, Hkv, D, qkv_dim, qkv_dim, HD, paged_prefill ? kc[l] : nullptr,
                                          paged_prefill ? vc[l] : nullptr, paged_prefill ? d_tables : nullptr, table_cap,
                                          &layout, scale, NVLLM_BF16, st)); ++launches;
+      mark(paged_prefill ? "prefill_attention (paged prefix)" : "prefill_attention");
     }
-    RUN(gemm(proj, attn, w.o, hidden, HD, hidden, NVLLM_BF16));
+    RUN(gemm(proj, attn, w.o, hidden, HD, hidden, NVLLM_BF16, "o_proj GEMM"));
     RUN(add_norm(w.post_ln));                                                                                          // qwen3.rs:382-385
     // gate_up GEMM with the SiLU*mul in its epilogue (MergedColumnParallelLinear + SiluAndMul, qwen3.rs:307-310)
     RUN(nvllm_gemm_silu_mul_bf16(act, normed, w.gate_up, N, inter, hidden, hidden, hidden, inter, gate_up,
                                  static_cast<size_t>(max_tokens) * 2 * inter * 2, st));
     launches += (inter % 128 == 0) ? 1 : 2;
-    RUN(gemm(proj, act, w.down, hidden, inter, hidden, NVLLM_BF16));
+    mark("gate_up_proj GEMM + SiLU*mul");
+    RUN(gemm(proj, act, w.down, hidden, inter, hidden, NVLLM_BF16, "down_proj GEMM"));
   }
   RUN(add_norm(final_norm));                                                                                           // qwen3.rs:389,501
   const bf16* head_in = normed;
   int rows = N;
   if (is_prefill) {  // only the last token of each sequence feeds the head (embed_head.rs:250-289)
-    RUN(nvllm_gather_last_tokens(last_hidden, normed, d_cu_q, S, hidden, NVLLM_BF16, st)); ++launches;
+    RUN(nvllm_gather_last_tokens(last_hidden, normed, d_cu_q, S, hidden, NVLLM_BF16, st)); ++launches; mark("gather_last_tokens");
     head_in = last_hidden;
     rows = S;
   }
   ++launches;
   RUN(nvllm_gemm_bf16(logits, head_in, lm_head, rows, vshard, hidden, hidden, hidden, vshard, NVLLM_F32, nullptr, 0, st));
+  mark("lm_head GEMM");
   if (tp == 1) {
-    RUN(nvllm_argmax(tokens, nullptr, logits, rows, vshard, vshard, 0, NVLLM_F32, st)); ++launches;
+    RUN(nvllm_argmax(tokens, nullptr, logits, rows, vshard, vshard, 0, NVLLM_F32, st)); ++launches; mark("argmax");
   } else {  // sharded argmax: local (max, id) -> all-gather -> first-max combine
     RUN(nvllm_argmax(local_ids, local_max, logits, rows, vshard, vshard, static_cast<int64_t>(rank) * vshard, NVLLM_F32, st));
     RUN(nvllm_allgather(comm, local_max, all_max, sizeof(float) * rows, st));
     RUN(nvllm_allgather(comm, local_ids, all_ids, sizeof(int64_t) * rows, st));
     RUN(nvllm_argmax_combine(tokens, all_max, all_ids, tp, rows, st));
     launches += 4;
+    mark("sharded argmax (argmax + 2 all-gathers + combine)");
   }
   return 0;
 }
@@ -580,6 +624,8 @@ int nvllm_runner::sample(const nvllm_batch& b) {
 
 int nvllm_runner::fetch(int64_t* out, int n) {
   NVLLM_CUDA(cudaStreamSynchronize(stream));
+  if (!prof_marks.empty()) prof_collect();
+  if (comm != nullptr) RUN(nvllm_comm_error(comm));  // a fused TP kernel gave up waiting for a peer: tokens are garbage
   if (out) memcpy(out, h_tokens, sizeof(int64_t) * n);
   return 0;
 }
@@ -633,6 +679,29 @@ int nvllm_runner_execute(nvllm_runner* r, const nvllm_batch* b, int64_t* h_token
   return r->fetch(h_tokens, b->num_seqs);
 }
 void* nvllm_runner_stream(nvllm_runner* r) { return r ? r->stream : nullptr; }
+int nvllm_runner_profile(nvllm_runner* r, int32_t enable) {
+  NVLLM_CHECK_ARG(r, NVLLM_ERR_ARG, "runner_profile: NULL");
+  NVLLM_CUDA(cudaStreamSynchronize(r->stream));
+  if (!r->prof_marks.empty()) r->prof_collect();
+  if (enable && !r->profiling) r->prof_acc.clear();
+  r->profiling = enable != 0;
+  return 0;
+}
+int64_t nvllm_runner_profile_report(nvllm_runner* r, char* h_buf, size_t cap) {
+  if (!r) return 0;
+  std::string out;
+  char line[256];
+  for (const auto& kv : r->prof_acc) {
+    snprintf(line, sizeof(line), "%s\t%lld\t%.3f\n", kv.first.c_str(), (long long)kv.second.second, kv.second.first);
+    out += line;
+  }
+  if (h_buf && cap > 0) {
+    const size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+    memcpy(h_buf, out.data(), n);
+    h_buf[n] = 0;
+  }
+  return static_cast<int64_t>(out.size());
+}
 int64_t nvllm_runner_last_launches(const nvllm_runner* r) { return r ? r->last_launches : 0; }
 int nvllm_runner_kv_cache(nvllm_runner* r, int32_t layer, void** k_cache, void** v_cache, nvllm_kv_layout* layout) {
   NVLLM_CHECK_ARG(r && layer >= 0 && layer < r->layers, NVLLM_ERR_ARG, "runner_kv_cache: layer %d", layer);

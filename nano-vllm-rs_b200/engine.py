@@ -70,6 +70,8 @@ ENGINE_PROTOTYPES = {
     "nvllm_runner_execute_async": (i32, [vp, C.POINTER(CBatch)]),
     "nvllm_runner_fetch_tokens": (i32, [vp, vp, i32]),
     "nvllm_runner_stream": (vp, [vp]),
+    "nvllm_runner_profile": (i32, [vp, i32]),
+    "nvllm_runner_profile_report": (i64, [vp, C.c_char_p, C.c_size_t]),
     "nvllm_runner_last_launches": (i64, [vp]),
     "nvllm_runner_kv_cache": (i32, [vp, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(_ffi.KvLayout)]),
     "nvllm_runner_time_decode_attention": (i32, [vp, i32, C.POINTER(f32), C.POINTER(i64)]),
@@ -298,6 +300,21 @@ class ModelRunner:
         check(lib().nvllm_runner_execute(self.h, C.byref(batch.c), toks.ctypes.data,
                                          logits.ctypes.data if return_logits else None))
         return (toks, logits) if return_logits else toks
+
+    def profile(self, enable=True):
+        """Start (clearing the accumulators) / stop the per-launch CUDA-event profile of eager steps."""
+        check(lib().nvllm_runner_profile(self.h, int(enable)))
+
+    def profile_report(self):
+        """{kernel name: (launches, total_us)} accumulated since profile(True)."""
+        n = lib().nvllm_runner_profile_report(self.h, None, 0)
+        buf = C.create_string_buffer(int(n) + 1)
+        lib().nvllm_runner_profile_report(self.h, buf, n + 1)
+        out = {}
+        for line in buf.value.decode().splitlines():
+            name, calls, us = line.split("\t")
+            out[name] = (int(calls), float(us))
+        return out
 
     def last_launches(self):
         return lib().nvllm_runner_last_launches(self.h)

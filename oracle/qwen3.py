@@ -17,6 +17,10 @@ ARCHS = {
                        num_attention_heads=16, num_key_value_heads=8, head_dim=128, tie_word_embeddings=True),
     "qwen3-8b": dict(vocab_size=151936, hidden_size=4096, intermediate_size=12288, num_hidden_layers=36,
                      num_attention_heads=32, num_key_value_heads=8, head_dim=128, tie_word_embeddings=False),
+    "qwen3-32b": dict(vocab_size=151936, hidden_size=5120, intermediate_size=25600, num_hidden_layers=64,
+                      num_attention_heads=64, num_key_value_heads=8, head_dim=128, tie_word_embeddings=False),
+    "qwen3-0.6b-2l": dict(vocab_size=2048, hidden_size=1024, intermediate_size=3072, num_hidden_layers=2,
+                          num_attention_heads=16, num_key_value_heads=8, head_dim=128, tie_word_embeddings=False),
     "tiny-tp8": dict(vocab_size=2048, hidden_size=512, intermediate_size=1024, num_hidden_layers=2,
                      num_attention_heads=16, num_key_value_heads=8, head_dim=128, tie_word_embeddings=False),
     "tiny": dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,

@@ -16,6 +16,10 @@ from oracle.bf16 import round_bf16  # noqa: E402
 CFG = dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
            num_key_value_heads=2, head_dim=128, max_position_embeddings=4096, rms_norm_eps=1e-6, rope_theta=1e6,
            tie_word_embeddings=False)
+# second fixture (qwen3_hf_wide.json): two layers at the REAL Qwen3-0.6B widths (hidden 1024, 16/8 heads of 128, inter 3072),
+# vocabulary cut to 2048 to keep the fixture small — arch "qwen3-0.6b-2l" of nvllm_config_init / oracle.qwen3.ARCHS
+CFG_WIDE = dict(CFG, vocab_size=2048, hidden_size=1024, intermediate_size=3072, num_attention_heads=16, num_key_value_heads=8)
+CFGS = {"tiny": (CFG, "qwen3_hf.json"), "wide": (CFG_WIDE, "qwen3_hf_wide.json")}
 SEED, STD = 20261104, 0.05
 PROMPTS = [[5, 17, 900, 3, 44], [1023, 0, 7, 7, 512, 64, 33, 2, 81, 300, 11, 640]]
 FORCED = [[10, 20, 30], [700, 5, 999]]   # tokens appended at the three decode steps (teacher forcing)
@@ -24,8 +28,9 @@ PREFIX = [(i * 37 + 11) % 1024 for i in range(32)]
 SUFFIXES = [[3, 1, 4, 1, 5], [9, 2, 6, 5, 3, 5, 8, 9, 7]]
 
 
-def make_weights():
+def make_weights(which="tiny"):
     """name -> f32 array of bf16-representable values; norm weights 1 + 0.1 N(0,1)."""
+    CFG = CFGS[which][0]
     rng = np.random.default_rng(SEED)
     H, Hkv, D, hid, I, V = (CFG[k] for k in ("num_attention_heads", "num_key_value_heads", "head_dim", "hidden_size",
                                              "intermediate_size", "vocab_size"))
@@ -42,12 +47,13 @@ def make_weights():
     return w
 
 
-def main():
+def main(which="tiny"):
     import torch
     from transformers import Qwen3Config, Qwen3ForCausalLM
+    CFG, fname = CFGS[which]
     cfg = Qwen3Config(attention_bias=False, attn_implementation="eager", **CFG)
     model = Qwen3ForCausalLM(cfg).eval().float()
-    w = make_weights()
+    w = make_weights(which)
     sd = model.state_dict()
     assert set(sd) == set(w), set(sd) ^ set(w)
     model.load_state_dict({k: torch.from_numpy(v) for k, v in w.items()})
@@ -64,9 +70,14 @@ def main():
         out["prefix"] = {"prefix": PREFIX, "suffixes": SUFFIXES,
                          "logits": [[float(x) for x in model(torch.tensor([PREFIX + sfx])).logits[0, -1].double().numpy()]
                                     for sfx in SUFFIXES]}
-    json.dump(out, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "qwen3_hf.json"), "w"))
-    print("wrote qwen3_hf.json", len(out["steps"]), "steps")
+    if which != "tiny":   # the wide fixture stores 6 significant digits (tolerances are ~1e-2 of a logit's sigma)
+        rnd = lambda rows: [[float(f"{x:.6g}") for x in r] for r in rows]
+        out["steps"] = [rnd(st) for st in out["steps"]]
+        out["prefix"]["logits"] = rnd(out["prefix"]["logits"])
+    json.dump(out, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), fname), "w"))
+    print("wrote", fname, len(out["steps"]), "steps")
 
 
 if __name__ == "__main__":
-    main()
+    for which in (sys.argv[1:] or ["tiny", "wide"]):
+        main(which)

@@ -13,22 +13,32 @@ from oracle import qwen3 as Q
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = json.load(open(os.path.join(HERE, "golden", "qwen3_hf.json")))
+GOLD_WIDE = json.load(open(os.path.join(HERE, "golden", "qwen3_hf_wide.json")))   # two layers at the real Qwen3-0.6B widths
 # same bound as the GPU-vs-oracle tests (tests/test_gpu_engine.py): bf16 rounding noise growing with sqrt(depth)
 LOGIT_SIGMA_PER_SQRT_LAYER, LOGIT_RTOL = 0.035, 1.6e-2
 
 
-def _weights():
+def _weights(which="tiny"):
     spec = importlib.util.spec_from_file_location("mk", os.path.join(HERE, "golden", "make_qwen3_hf_golden.py"))
     mk = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mk)
-    assert mk.CFG == GOLD["config"] and mk.SEED == GOLD["seed"]
-    return mk.make_weights()
+    gold = GOLD if which == "tiny" else GOLD_WIDE
+    assert mk.CFGS[which][0] == gold["config"] and mk.SEED == gold["seed"]
+    return mk.make_weights(which)
 
 
-def test_oracle_model_matches_hf_qwen3_prefill_and_decode():
+import pytest  # noqa: E402
+
+
+@pytest.mark.parametrize("which", ["tiny", "wide"])
+def test_oracle_model_matches_hf_qwen3_prefill_and_decode(which):
+    GOLD = globals()["GOLD"] if which == "tiny" else GOLD_WIDE
+    # bf16 rounding noise of the oracle vs HF's fp32: rms 0.005 sigma (tiny) / 0.011 sigma (width 1024, K up to 3072); the
+    # bound is on the MAX over all logits (4-5 rms), so the wide fixture states 0.05 * sqrt(layers) (observed max 0.053)
+    LOGIT_SIGMA_PER_SQRT_LAYER = 0.035 if which == "tiny" else 0.05
     cfg = dict(GOLD["config"], qk_norm=True)
     bs = 16
-    oracle = Q.Qwen3Oracle(cfg, _weights(), num_blocks=8, block_size=bs)
+    oracle = Q.Qwen3Oracle(cfg, _weights(which), num_blocks=8, block_size=bs)
     sched = H.Scheduler(H.Config(kvcache_block_size=bs, num_kvcache_blocks=8, max_num_batched_tokens=256, max_num_seqs=8))
     n_dec = len(GOLD["forced"][0])
     seqs = [H.Sequence(p, H.SamplingParams(temperature=0.0, max_tokens=n_dec + 1, ignore_eos=True), block_size=bs)
@@ -54,7 +64,7 @@ def test_oracle_model_matches_hf_qwen3_prefill_and_decode():
         forced = [f[step] if step < n_dec else 0 for f in GOLD["forced"]]
         sched.postprocess(batch, forced)
     print("max |oracle - HF| =", worst, "sigma")
-    assert worst < 0.05   # observed ~0.01-0.02: pure bf16 rounding noise; a wiring error shows up as O(1) sigma
+    assert worst < (0.05 if which == "tiny" else 0.075)   # observed ~0.01-0.02: pure bf16 rounding noise; a wiring error shows up as O(1) sigma
 
 
 def test_wiring_errors_would_be_caught():
