@@ -206,6 +206,11 @@ int nvllm_argmax(int64_t* out_ids, float* out_max, const void* logits, int32_t b
  * lowest shard on ties (== first maximum over the concatenated vocab). */
 int nvllm_argmax_combine(int64_t* out_ids, const float* all_max, const int64_t* all_ids,
                          int32_t tp, int32_t batch, void* stream);
+/* Puts the all-gathered vocab shards of a tensor-parallel LM head back into full rows — the gather the reference leaves as
+ * a TODO (src/layers/embed_head.rs:321-336): out[b, r*vshard + j] = gathered[r, b, j] (f32).  With it every rank holds the
+ * full [rows, vocab] logits and runs the same deterministic nvllm_sample: temperature / top-k / top-p under TP. */
+int nvllm_assemble_vocab_shards(float* out, const float* gathered, int32_t tp, int32_t rows, int32_t vshard,
+                                void* stream);
 
 /* K12 — replaces Sampler::forward / batch_sample / sample_single (src/layers/sampler.rs:26-106,221-254) with its
  * helpers apply_top_k (:115-149), apply_top_p (:152-191), multinomial_sample (:194-203) and sample_gumbel (:205-219)

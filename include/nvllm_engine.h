@@ -50,9 +50,9 @@ int nvllm_config_init(nvllm_config* cfg, const char* arch);
 int nvllm_config_validate(const nvllm_config* cfg);
 
 /* SamplingParams (sampling_params.rs:10-88).  temperature == 0 is greedy (sampler.rs:79-81); otherwise temperature /
- * top-k / top-p / Gumbel-max sampling runs on the device (nvllm_sample) with tensor_parallel_size == 1 — under TP the
- * logits are vocab-sharded and only greedy decoding is wired (rejected loudly otherwise).  repetition_penalty is carried
- * but unused, as in the reference (sampler.rs:26-67 never reads it). */
+ * top-k / top-p / Gumbel-max sampling runs on the device (nvllm_sample).  Under tensor parallelism the vocab-sharded
+ * logits are all-gathered and re-assembled (nvllm_assemble_vocab_shards) so that every rank samples the same token from
+ * the same full rows.  repetition_penalty is carried but unused, as in the reference (sampler.rs:26-67 never reads it). */
 typedef struct nvllm_sampling_params {
   float temperature; /* reference default 1.0 */
   int32_t max_tokens; /* 64 */

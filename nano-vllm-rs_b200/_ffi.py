@@ -58,6 +58,7 @@ PROTOTYPES = {
     "nvllm_gather_last_tokens": (i32, [vp, vp, vp, i32, i32, i32, vp]),
     "nvllm_argmax": (i32, [vp, vp, vp, i32, i32, i64, i64, i32, vp]),
     "nvllm_argmax_combine": (i32, [vp, vp, vp, i32, i32, vp]),
+    "nvllm_assemble_vocab_shards": (i32, [vp, vp, i32, i32, i32, vp]),
     "nvllm_sample": (i32, [vp, vp, i32, i32, i64, vp, vp, vp, vp, vp, vp, vp]),
     "nvllm_comm_unique_id": (i32, [vp]),
     "nvllm_comm_init": (i32, [C.POINTER(vp), vp, i32, i32]),

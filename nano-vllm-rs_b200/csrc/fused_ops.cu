@@ -522,6 +522,40 @@ extern "C" int nvllm_argmax_combine(int64_t* out_ids, const float* all_max, cons
   return 0;
 }
 
+// out[b, r * vshard + j] = in[r, b, j]: the all-gathered vocab shards of a tensor-parallel LM head put back into full rows
+// (the gather the reference leaves as a TODO, embed_head.rs:321-336).  16-byte vectors when vshard % 4 == 0.
+namespace nvllm {
+__global__ void assemble_vocab_shards_kernel(float* __restrict__ out, const float* __restrict__ in, int tp, int rows,
+                                             int vshard, int64_t total_vec, int vec) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int per_row = vshard / vec;  // vectors per (rank, row)
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total_vec;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t rb = i / per_row;            // r * rows + b
+    const int j = static_cast<int>(i - rb * per_row);
+    const int r = static_cast<int>(rb / rows), b = static_cast<int>(rb - static_cast<int64_t>(r) * rows);
+    const int64_t dst = (static_cast<int64_t>(b) * tp + r) * vshard + static_cast<int64_t>(j) * vec;
+    if (vec == 4) *reinterpret_cast<uint4*>(out + dst) = ld_nc_16(in + i * 4);
+    else out[dst] = in[i];
+  }
+}
+}  // namespace nvllm
+
+extern "C" int nvllm_assemble_vocab_shards(float* out, const float* gathered, int32_t tp, int32_t rows, int32_t vshard,
+                                           void* stream) {
+  using namespace nvllm;
+  NVLLM_CHECK_ARG(tp > 0 && rows >= 0 && vshard > 0, NVLLM_ERR_ARG, "assemble_vocab_shards: sizes");
+  if (rows == 0) return 0;
+  NVLLM_CHECK_ARG(out && gathered && out != gathered, NVLLM_ERR_ARG, "assemble_vocab_shards: pointers");
+  const int vec = (vshard % 4 == 0 && aligned16(out) && aligned16(gathered)) ? 4 : 1;
+  const int64_t total_vec = static_cast<int64_t>(tp) * rows * (vshard / vec);
+  NVLLM_CUDA(launch_pdl(assemble_vocab_shards_kernel, dim3(grid_for(total_vec, 256, 8)), dim3(256), 0,
+                        static_cast<cudaStream_t>(stream), out, gathered, static_cast<int>(tp), static_cast<int>(rows),
+                        static_cast<int>(vshard), total_vec, vec));
+  return 0;
+}
+
 extern "C" int nvllm_init_weight(void* w, int64_t count, uint64_t seed, uint64_t tensor_id, float std,
                                  int32_t dtype, void* stream) {
   NVLLM_CHECK_ARG(count >= 0, NVLLM_ERR_ARG, "init_weight: count");

@@ -88,6 +88,7 @@ struct nvllm_runner {
   bf16 *h = nullptr, *normed = nullptr, *qkv = nullptr, *attn = nullptr, *proj = nullptr, *gate_up = nullptr,
        *act = nullptr, *last_hidden = nullptr;
   float* logits = nullptr;
+  float *gathered_logits = nullptr, *full_logits = nullptr;  // tp > 1: [tp, seqs, V/tp] all-gathered, then [seqs, V] (sampling)
   float *local_max = nullptr, *all_max = nullptr;
   int64_t *local_ids = nullptr, *all_ids = nullptr, *tokens = nullptr;
   void* decode_ws = nullptr;
@@ -260,6 +261,10 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   RUN(dalloc(&gate_up, T * 2 * inter)); RUN(dalloc(&act, T * inter));
   RUN(dalloc(&last_hidden, static_cast<size_t>(max_seqs) * hidden));
   RUN(dalloc(&logits, static_cast<size_t>(max_seqs) * vshard));
+  if (tp > 1) {
+    RUN(dalloc(&gathered_logits, static_cast<size_t>(max_seqs) * vocab));
+    RUN(dalloc(&full_logits, static_cast<size_t>(max_seqs) * vocab));
+  }
   RUN(dalloc(&tokens, max_seqs)); RUN(dalloc(&local_ids, max_seqs)); RUN(dalloc(&local_max, max_seqs));
   RUN(dalloc(&all_ids, static_cast<size_t>(max_seqs) * tp)); RUN(dalloc(&all_max, static_cast<size_t>(max_seqs) * tp));
   // split-K workspace: the largest any decode bucket can ask for
@@ -553,9 +558,6 @@ int nvllm_runner::execute_async(const nvllm_batch& b) {
   NVLLM_CHECK_ARG(b.num_seqs > 0 && b.num_tokens > 0, NVLLM_ERR_ARG, "execute: empty batch");
   bool sampled = false;
   for (int i = 0; i < b.num_seqs && b.temperatures != nullptr; ++i) sampled |= b.temperatures[i] != 0.0f;
-  // Under TP the logits are vocab-sharded and only the (max, id) combine of greedy decoding is wired across ranks.
-  NVLLM_CHECK_ARG(!sampled || tp == 1, NVLLM_ERR_STATE,
-                  "execute: temperature != 0 needs tensor_parallel_size == 1 (only greedy sampling is wired under TP)");
   if (b.is_prefill) {
     RUN(upload(b, 0));
     RUN(forward(b.num_tokens, b.num_seqs, true, b.has_block_tables != 0, b));
@@ -617,6 +619,16 @@ int nvllm_runner::sample(const nvllm_batch& b) {
   }
   NVLLM_CUDA(cudaMemcpyAsync(d_samp, h_samp, 24 * S, cudaMemcpyHostToDevice, stream));
   ++last_launches;
+  if (tp > 1) {
+    // Vocab-sharded head (embed_head.rs:321-336 TODO): all-gather the f32 shards, put the rows back together, and run the
+    // SAME deterministic sampler on the full rows on every rank — identical tokens everywhere, no token broadcast.
+    RUN(nvllm_allgather(comm, logits, gathered_logits, sizeof(float) * n * vshard, stream));
+    RUN(nvllm_assemble_vocab_shards(full_logits, gathered_logits, tp, b.num_seqs, vshard, stream));
+    last_launches += 2;
+    return nvllm_sample(tokens, full_logits, b.num_seqs, vocab, vocab, reinterpret_cast<const float*>(d_samp),
+                        reinterpret_cast<const int32_t*>(d_samp + 4 * S), reinterpret_cast<const float*>(d_samp + 8 * S),
+                        reinterpret_cast<const uint64_t*>(d_samp + 16 * S), nullptr, nullptr, stream);
+  }
   return nvllm_sample(tokens, logits, b.num_seqs, vshard, vshard, reinterpret_cast<const float*>(d_samp),
                       reinterpret_cast<const int32_t*>(d_samp + 4 * S), reinterpret_cast<const float*>(d_samp + 8 * S),
                       reinterpret_cast<const uint64_t*>(d_samp + 16 * S), nullptr, nullptr, stream);

@@ -175,8 +175,10 @@ def test_cfg4_shape_prefix_cached_prefill_then_decode_qwen3_0_6b(cuda):
     rng = np.random.default_rng(4321)
     prefix = rng.integers(0, 151936, 4096).tolist()
     prompts = [prefix + rng.integers(0, 151936, 256).tolist() for _ in range(3)]
-    stats, sched = run_lockstep("qwen3-0.6b", prompts, max_tokens=2, bs=256, num_blocks=32, std=0.02, max_num_seqs=8,
-                                max_model_len=8192, max_num_batched_tokens=8192)
+    # can_allocate demands free >= 17 blocks per sequence even though 16 will be cache hits (block_manager.rs:152-154), and
+    # admission counts the full 4352 tokens per sequence (scheduler.rs:135): 64 blocks / 16384 tokens admit all three at once
+    stats, sched = run_lockstep("qwen3-0.6b", prompts, max_tokens=2, bs=256, num_blocks=64, std=0.02, max_num_seqs=8,
+                                max_model_len=8192, max_num_batched_tokens=16384)
     print(stats, sched.get_stats())
     assert stats["prefill_steps"] == 1 and stats["decode_steps"] == 1 and stats["rows"] == 6
     assert stats["strict"] >= 5

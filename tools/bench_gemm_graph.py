@@ -5,7 +5,7 @@ graph is replayed; us/launch = replay time / launches.  Per-launch event timing 
 import argparse, json, os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from nano_vllm_rs_b200 import ops  # noqa: E402
+from nano_vllm_rs_b200 import _ffi, ops  # noqa: E402
 
 SHAPES = {  # name: (M, N, K, kind)
     "0.6B qkv": (256, 4096, 1024, "gemm"), "0.6B o": (256, 1024, 2048, "gemm"), "0.6B gate_up+silu": (256, 3072, 1024, "silu"),
@@ -63,6 +63,7 @@ def main():
             for k in ALL:
                 os.environ.pop(k, None)
             os.environ.update(kn)
+            _ffi.lib().nvllm_reload_env()   # the library parses its knobs once; sweeps re-parse explicitly
             try:
                 r = run(name, M, N, K, kind, a.layers, a.reps)
             except Exception as ex:  # a knob that does not apply to a shape
@@ -71,6 +72,7 @@ def main():
             print(json.dumps(r), flush=True)
     for k in ALL:
         os.environ.pop(k, None)
+    _ffi.lib().nvllm_reload_env()
 
 
 if __name__ == "__main__":
