@@ -98,6 +98,23 @@ int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache, 
                                  size_t workspace_bytes, int32_t num_splits, int32_t dtype,
                                  void* stream);
 
+/* K7 + K1 + K2 in ONE launch for decode steps — replaces, per layer, what Qwen3Attention::forward does between qkv_proj
+ * and o_proj (src/models/qwen3.rs:219-233): per-head q/k RMSNorm + RotaryEmbedding::forward
+ * (src/layers/rotary_embedding.rs:23-48,145-158), Attention::store_kv_cache (src/layers/attention.rs:150-174) and
+ * Attention::flash_attention_decode (:225-318).  qkv: the packed [q | k | v] rows of this step ([batch, (H+2Hkv)*D], read
+ * only — nothing is written back into it); the step's K (normed, rotated) and V rows are stored at slot_mapping[b] (< 0:
+ * skipped) and attended to from shared memory, so context_lens[b] COUNTS this step's token (context_lens - 1 tokens are
+ * read through block_tables).  Same rounding points as nvllm_qknorm_rope_store followed by nvllm_paged_decode_attention
+ * (bf16 after the norm, bf16 after the rotation); head_dim 128 only.  q_norm_w / k_norm_w NULL = no qk-norm. */
+int nvllm_paged_decode_attention_fused(void* out, const void* qkv, const int64_t* positions, const float* cos_sin,
+                                       const void* q_norm_w, const void* k_norm_w, float eps, int32_t max_position,
+                                       void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                                       const int32_t* block_tables, const int32_t* context_lens, int32_t batch,
+                                       int32_t num_heads, int32_t max_blocks_per_seq, int64_t qkv_token_stride,
+                                       int64_t out_token_stride, const nvllm_kv_layout* layout, float scale,
+                                       void* workspace, size_t workspace_bytes, int32_t num_splits, int32_t dtype,
+                                       void* stream);
+
 /* K3 / K4 — replaces Attention::flash_attention_varlen (+ create_causal_mask) and
  * flash_attention_varlen_with_cache (src/layers/attention.rs:177-222,321-339).
  * Causal attention per sequence i over q rows [cu_seqlens_q[i], cu_seqlens_q[i+1]) and keys

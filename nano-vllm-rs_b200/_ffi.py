@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libnvllm.so")
+# NVLLM_LIB_PATH: debug builds only (e.g. lib/libnvllm_timeline.so for tools/gemm_timeline.py); a missing file still raises
+LIB_PATH = os.environ.get("NVLLM_LIB_PATH") or os.path.join(_HERE, "lib", "libnvllm.so")
 _lib = None
 
 i32, i64, u64, f32, f64, vp, sz = C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_double, C.c_void_p, C.c_size_t
@@ -43,6 +44,8 @@ PROTOTYPES = {
     "nvllm_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "nvllm_paged_decode_choose_splits": (i32, [i32, i32, i32, i32]),
     "nvllm_paged_decode_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64, LP, f32, vp, sz, i32, i32, vp]),
+    "nvllm_paged_decode_attention_fused": (i32, [vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64,
+                                                 LP, f32, vp, sz, i32, i32, vp]),
     "nvllm_varlen_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64,
                                              vp, vp, vp, i32, LP, f32, i32, vp]),
     "nvllm_gemm_workspace_bytes": (sz, [i32, i32, i32]),

@@ -50,6 +50,7 @@ static void parse_knobs() {
   k.decode_cfg = num("NVLLM_DECODE_CFG", 0);
   k.prefill_poly = num("NVLLM_PREFILL_POLY", 4);
   k.fuse_rope = num("NVLLM_FUSE_ROPE", 0) == 1;
+  k.fuse_decode = num("NVLLM_FUSE_DECODE", 1);
   k.fused_tp = num("NVLLM_FUSED_TP", 1);
   k.profile = num("NVLLM_PROFILE", 0);
   if (const char* e = getenv("NVLLM_COMM_TIMEOUT_MS")) { const long long v = atoll(e); if (v > 0) k.comm_timeout_ms = v; }

@@ -61,6 +61,7 @@ struct Knobs {
   int decode_cfg = 0;       // NVLLM_DECODE_CFG: alternative (stages, warps) instantiations of the paged decode kernel
   int prefill_poly = 4;     // NVLLM_PREFILL_POLY: exp2 split of the prefill softmax
   int fuse_rope = 0;        // NVLLM_FUSE_ROPE: qkv GEMM epilogue with q/k-norm + RoPE + KV store
+  int fuse_decode = 1;      // NVLLM_FUSE_DECODE: 0 = separate qknorm_rope_store launch before the paged decode attention
   int fused_tp = 1;         // NVLLM_FUSED_TP: 0 = ncclAllReduce + separate add_rmsnorm
   int profile = 0;          // NVLLM_PROFILE: 1 = the runner times every launch of eager steps with CUDA events
   long long comm_timeout_ms = 600000;  // NVLLM_COMM_TIMEOUT_MS: peer-flag spin bound of the fused TP kernels

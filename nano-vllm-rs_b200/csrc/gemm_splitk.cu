@@ -15,6 +15,23 @@
 #include "tc.cuh"
 
 namespace nvllm {
+#ifdef NVLLM_TIMELINE
+// Debug build only (make timeline -> lib/libnvllm_timeline.so, tools/gemm_timeline.py): every CTA records %globaltimer at
+// its phase boundaries into a host-provided buffer, to decompose the fixed per-launch cost of the decode-sized GEMMs.
+__device__ unsigned long long* g_tl_buf = nullptr;   // [cap][12]: {blockIdx, t0..t9, smid}
+__device__ unsigned int g_tl_cursor = 0;
+__device__ unsigned int g_tl_cap = 0;
+__device__ __forceinline__ unsigned long long tl_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
+}
+#define TL_DECL __shared__ unsigned long long tl_s[12];
+#define TL(i) do { tl_s[i] = tl_now(); } while (0)
+#else
+#define TL_DECL
+#define TL(i) do { } while (0)
+#endif
 namespace {
 
 template <int BN>
@@ -77,6 +94,8 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   const int tile = static_cast<int>(blockIdx.x) / SK;
   const int m_tile = tile % num_m_tiles, n_tile = tile / num_m_tiles;
   const int kb_per = (K / C::BK) / SK, kb0 = rank * kb_per;
+  TL_DECL
+  if (threadIdx.x == 0) TL(0);   // kernel entry
   pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
@@ -93,6 +112,7 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if (threadIdx.x == 0) TL(1);   // prologue (barrier init, TMEM alloc) done
 
   if (warp == 0 && lane == 0) {
     // ===== TMA producer: weights first (independent of the predecessor kernel), x after the dependency wait =====
@@ -110,6 +130,7 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
       load_w(i, kb0 + i);
     }
     pdl_wait();
+    TL(2);   // predecessor kernel complete (x may be loaded)
     int stage = 0;
     uint32_t phase = 0;
     for (int i = 0; i < kb_per; ++i) {
@@ -126,8 +147,11 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     constexpr uint32_t idesc = umma_idesc_bf16(C::BM, BN, 0, 0);
     int stage = 0;
     uint32_t phase = 0;
+    pdl_wait();  // keep the wait for the predecessor out of the bounded mbarrier waits
     for (int i = 0; i < kb_per; ++i) {
       mbar_wait(full_bar(stage), phase);
+      if (i == 0) TL(3);             // first operand stage landed
+      if (i == kb_per - 1) TL(4);    // last operand stage landed
       tc_fence_after();
       const uint32_t a0 = sA + stage * C::kABytes, b0 = sB + stage * C::kBBytes;
 #pragma unroll
@@ -141,7 +165,9 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   } else if (warp >= 4) {
     // ===== park the partial tile: TMEM -> f32 shared memory, column-major (lanes = rows: conflict-free) =====
     const int q = warp & 3;
+    pdl_wait();               // (also needed below: y may still be read by an earlier kernel)
     mbar_wait(tfull_bar, 0);  // every MMA has retired: the operand ring is dead and can be overwritten
+    if (threadIdx.x == 128) TL(5);   // accumulator complete
     tc_fence_after();
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     const uint32_t prow = smem_base + (q * 32 + lane) * 4;
@@ -156,7 +182,9 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     tc_fence_before();
   }
   __syncwarp();
+  if (threadIdx.x == 128) TL(6);     // partial tile parked in shared memory
   cluster_sync_all();  // all SK partial tiles are parked and visible cluster-wide
+  if (threadIdx.x == 128) TL(7);     // first cluster barrier passed
 
   if (warp >= 4) {
     // ===== reduce this CTA's column slice over the cluster in fixed rank order, then the usual epilogue =====
@@ -232,11 +260,27 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     }
   }
   __syncwarp();
+  if (threadIdx.x == 128) TL(8);     // DSMEM reduce + global stores done
   cluster_sync_all();  // nobody leaves while a peer may still read its partial tile
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<C::kTmemCols>(tmem_base);
   }
+#ifdef NVLLM_TIMELINE
+  if (threadIdx.x == 128) TL(9);
+  __syncthreads();
+  if (threadIdx.x == 0 && g_tl_buf != nullptr) {
+    const unsigned int slot = atomicAdd(&g_tl_cursor, 1u);
+    if (slot < g_tl_cap) {
+      unsigned long long* e = g_tl_buf + static_cast<size_t>(slot) * 12;
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %%smid;\n" : "=r"(smid));
+      e[0] = blockIdx.x;
+      for (int i = 0; i < 10; ++i) e[1 + i] = tl_s[i];
+      e[11] = smid;
+    }
+  }
+#endif
 }
 
 // Stages of the operand ring: NVLLM_GEMM_SK_STAGES (benchmark knob) or the deepest that fits, never more than the
@@ -317,6 +361,18 @@ bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_
   const long waves_d = (tiles_d + sms - 1) / sms;
   return best * 10 < splitk_cost(bn_default, 1, k) * waves_d * 9;  // at least 10 % fewer bytes per SM
 }
+
+#ifdef NVLLM_TIMELINE
+}  // namespace nvllm
+extern "C" int nvllmdbg_timeline(unsigned long long* d_buf, unsigned int cap) {
+  unsigned int zero = 0;
+  if (cudaMemcpyToSymbol(nvllm::g_tl_buf, &d_buf, sizeof(d_buf)) != cudaSuccess) return 1;
+  if (cudaMemcpyToSymbol(nvllm::g_tl_cap, &cap, sizeof(cap)) != cudaSuccess) return 1;
+  if (cudaMemcpyToSymbol(nvllm::g_tl_cursor, &zero, sizeof(zero)) != cudaSuccess) return 1;
+  return 0;
+}
+namespace nvllm {
+#endif
 
 int gemm_splitk_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw, int64_t ldy,
                          bool silu, int bn, int sk, cudaStream_t st) {

@@ -183,6 +183,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     constexpr uint32_t idesc = umma_idesc_bf16(C::BM, BN, 0, 0);
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
+    pdl_wait();  // no operand can land before the predecessor is done: keep that wait out of the bounded mbarrier waits
     for (int tile = cta0; tile < num_tiles; tile += cta_stride) {
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);  // epilogue has drained this TMEM buffer
       tc_fence_after();

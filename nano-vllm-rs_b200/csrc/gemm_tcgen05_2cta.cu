@@ -117,6 +117,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmap_x, const __gri
     constexpr uint32_t idesc = umma_idesc_bf16(C::BM, BN, 0, 0);
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
+    pdl_wait();  // keep the wait for the predecessor out of the bounded mbarrier waits
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);
       tc_fence_after();

@@ -121,6 +121,7 @@ struct nvllm_runner {
   std::vector<cudaEvent_t> prof_pool;
   std::map<std::string, std::pair<double, int64_t>> prof_acc;  // name -> (total us, launches)
   bool fuse_rope = false; // NVLLM_FUSE_ROPE=1: qkv GEMM epilogue does q/k norm + RoPE + KV store for decode-sized batches
+  bool fuse_decode = true; // decode: q/k-norm + RoPE + KV store inside the paged attention kernel (NVLLM_FUSE_DECODE=0: separate)
   bool fused_tp = false;  // h / normed / proj live in NVLink-mapped symmetric memory; all-reduce fused with add + RMSNorm
 
   ~nvllm_runner() {
@@ -217,6 +218,7 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   else { layout.token_stride = D; layout.head_stride = static_cast<int64_t>(bs) * D; }                     // head-major
 
   fuse_rope = knobs().fuse_rope != 0;
+  fuse_decode = knobs().fuse_decode != 0 && c.head_dim == 128;
   NVLLM_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   // weights
   RUN(dalloc(&embed, static_cast<size_t>(vocab) * hidden));
@@ -493,25 +495,37 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
     // (and, under TP, with the all-reduce of that output: see add_norm below)
     if (l == 0) { RUN(nvllm_add_rmsnorm(normed, h, nullptr, w.input_ln, N, hidden, eps, NVLLM_BF16, st)); ++launches; mark("add_rmsnorm"); }
     else RUN(add_norm(w.input_ln));
+    const bf16* qnw = cfg.qk_norm ? w.q_norm : nullptr;
+    const bf16* knw = cfg.qk_norm ? w.k_norm : nullptr;
+    bool roped = false;  // q/k-norm + RoPE + KV store already applied to the qkv buffer / cache
     if (fuse_rope && D == 128 && N <= 256) {
       // decode-sized batches: qkv GEMM with q/k norm + RoPE + KV-cache store in its epilogue (one head per 128-wide tile)
       ++launches;
-      RUN(nvllm_gemm_qkv_rope_store(qkv, normed, w.qkv, N, hidden, hidden, hidden, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr,
-                                    cfg.qk_norm ? w.k_norm : nullptr, eps, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l],
-                                    d_slots, &layout, st));
+      RUN(nvllm_gemm_qkv_rope_store(qkv, normed, w.qkv, N, hidden, hidden, hidden, d_pos, rope, qnw, knw, eps, H, Hkv, D,
+                                    cfg.max_position_embeddings, kc[l], vc[l], d_slots, &layout, st));
       mark("qkv_proj GEMM + rope/store epilogue");
+      roped = true;
     } else {
       RUN(gemm(qkv, normed, w.qkv, qkv_dim, hidden, qkv_dim, NVLLM_BF16, "qkv_proj GEMM"));
-      // q/k norm + RoPE in place, K/V of this step into the cache (store before attention: note N2)
-      RUN(nvllm_qknorm_rope_store(qkv, d_pos, rope, cfg.qk_norm ? w.q_norm : nullptr, cfg.qk_norm ? w.k_norm : nullptr, eps,
-                                  N, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l], d_slots, &layout, NVLLM_BF16, st)); ++launches;
-      mark("qknorm_rope_store");
+      if (is_prefill || !fuse_decode) {
+        // q/k norm + RoPE in place, K/V of this step into the cache (store before attention: note N2)
+        RUN(nvllm_qknorm_rope_store(qkv, d_pos, rope, qnw, knw, eps, N, H, Hkv, D, cfg.max_position_embeddings, kc[l], vc[l],
+                                    d_slots, &layout, NVLLM_BF16, st)); ++launches;
+        mark("qknorm_rope_store");
+        roped = true;
+      }
     }
     if (!is_prefill) {
-      RUN(nvllm_paged_decode_attention(attn, qkv, kc[l], vc[l], d_tables, d_ctx, N, H, table_cap, qkv_dim, HD, &layout,
-                                       scale, decode_ws, decode_ws_bytes, splits, NVLLM_BF16, st));
+      if (!roped) {  // one launch: q/k-norm + RoPE + KV store + split-K paged attention (qwen3.rs:219-233)
+        RUN(nvllm_paged_decode_attention_fused(attn, qkv, d_pos, rope, qnw, knw, eps, cfg.max_position_embeddings, kc[l], vc[l],
+                                               d_slots, d_tables, d_ctx, N, H, table_cap, qkv_dim, HD, &layout, scale,
+                                               decode_ws, decode_ws_bytes, splits, NVLLM_BF16, st));
+      } else {
+        RUN(nvllm_paged_decode_attention(attn, qkv, kc[l], vc[l], d_tables, d_ctx, N, H, table_cap, qkv_dim, HD, &layout,
+                                         scale, decode_ws, decode_ws_bytes, splits, NVLLM_BF16, st));
+      }
       launches += splits > 1 ? 2 : 1;
-      mark("paged_decode_attention");
+      mark(roped ? "paged_decode_attention" : "paged_decode_attention (+ q/k-norm, RoPE, KV store)");
     } else {
       RUN(nvllm_varlen_prefill_attention(attn, qkv, qkv + HD, qkv + HD + Hkv * D, d_cu_q, d_cu_k, S, N, N, b.max_seqlen_q,
                                          b.max_seqlen_k, H, Hkv, D, qkv_dim, qkv_dim, HD, paged_prefill ? kc[l] : nullptr,
@@ -756,7 +770,16 @@ int nvllm_runner_time_decode_attention(nvllm_runner* r, int32_t iters, float* ms
   NVLLM_CHECK_ARG(r->last_decode_b > 0 && r->d_ctx != nullptr, NVLLM_ERR_STATE, "time_decode_attention: no decode step has run yet");
   const int B = r->last_decode_b, HD = r->H * r->D;
   const float scale = 1.0f / sqrtf(static_cast<float>(r->D));
+  const bool fused = r->fuse_decode && !(r->fuse_rope && r->D == 128 && B <= 256);  // the kernel the decode step launches
   auto launch = [&](int l) {
+    if (fused) {  // re-stores the step's K/V rows into the same slots: idempotent
+      const auto& w = r->lw[l];
+      return nvllm_paged_decode_attention_fused(r->attn, r->qkv, r->d_pos, r->rope, r->cfg.qk_norm ? w.q_norm : nullptr,
+                                                r->cfg.qk_norm ? w.k_norm : nullptr, r->cfg.rms_norm_eps,
+                                                r->cfg.max_position_embeddings, r->kc[l], r->vc[l], r->d_slots, r->d_tables,
+                                                r->d_ctx, B, r->H, r->table_cap, r->qkv_dim, HD, &r->layout, scale,
+                                                r->decode_ws, r->decode_ws_bytes, r->last_decode_splits, NVLLM_BF16, r->stream);
+    }
     return nvllm_paged_decode_attention(r->attn, r->qkv, r->kc[l], r->vc[l], r->d_tables, r->d_ctx, B, r->H, r->table_cap,
                                         r->qkv_dim, HD, &r->layout, scale, r->decode_ws, r->decode_ws_bytes,
                                         r->last_decode_splits, NVLLM_BF16, r->stream);

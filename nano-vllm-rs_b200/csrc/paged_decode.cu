@@ -43,6 +43,17 @@ struct DecodeParams {
   int batch, H, Hkv, g, ngrp, max_blocks, block_size, num_splits;
   int64_t q_stride, out_stride, blk_stride, tok_stride, head_stride;
   float scale_log2;
+  // FUSE only (nvllm_paged_decode_attention_fused): q points at the packed [q | k | v] rows of this step; the kernel applies
+  // q/k-norm + RoPE itself, writes the step's K/V row into the cache and attends to it from shared memory.
+  bf16* kc_w;
+  bf16* vc_w;
+  const bf16* qnw;       // may be NULL (no qk-norm)
+  const bf16* knw;
+  const float* cos_sin;  // [max_position, D]: D/2 cosines then D/2 sines per position
+  const int64_t* pos;
+  const int32_t* slots;
+  float eps;
+  int max_position;
 };
 
 template <int D, int STAGES, int NWARPS>
@@ -60,7 +71,13 @@ struct DecodeCfg {
   static constexpr int kRowStep = 32 / kChunks;
 };
 
-template <int D, int STAGES, int NWARPS>
+// FUSE == true: Qwen3Attention::forward's per-head q/k RMSNorm + RotaryEmbedding::forward (qwen3.rs:219-229,
+// rotary_embedding.rs:23-48) and Attention::store_kv_cache (attention.rs:150-174) run inside this kernel: every warp norms
+// and rotates its Q fragments in registers; the context seen through the cache is context_lens - 1 tokens; warp 0 of the
+// CTA owning the last non-empty split builds the step's own K (normed, rotated) / V row, stores it at slot_mapping[b] and
+// processes it as one extra 16-token tile (rows 1..15 masked) straight from shared memory.  Same rounding points as the
+// stand-alone qknorm_rope_store kernel (bf16 after the norm, bf16 after the rotation).
+template <int D, int STAGES, int NWARPS, bool FUSE>
 __global__ void __launch_bounds__(NWARPS * 32, (DecodeCfg<D, STAGES, NWARPS>::kSmemBytes <= 72 * 1024) ? 3 : (DecodeCfg<D, STAGES, NWARPS>::kSmemBytes <= 110 * 1024) ? 2 : 1)
 paged_decode_kernel(const DecodeParams p) {
   using C = DecodeCfg<D, STAGES, NWARPS>;
@@ -75,7 +92,8 @@ paged_decode_kernel(const DecodeParams p) {
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   pdl_wait();  // q and the newest KV row were written by the previous kernel
-  const int ctx = __ldg(p.ctx + b);
+  const int ctx_all = __ldg(p.ctx + b);        // tokens attended to, including (FUSE) this step's own
+  const int ctx = FUSE ? max(ctx_all - 1, 0) : ctx_all;  // tokens read from the cache
   const int gvalid = min(8, p.g - grp * 8);   // q heads handled by this CTA
   const int qh0 = kvh * p.g + grp * 8;         // first q head
 
@@ -97,6 +115,55 @@ paged_decode_kernel(const DecodeParams p) {
       const int d0 = ks * 16 + (lane & 3) * 2;
       qb[ks][0] = hv ? *reinterpret_cast<const uint32_t*>(qrow + d0) : 0u;
       qb[ks][1] = hv ? *reinterpret_cast<const uint32_t*>(qrow + d0 + 8) : 0u;
+    }
+    if constexpr (FUSE) {
+      static_assert(!FUSE || D == 128, "fused q/k-norm + RoPE: head_dim 128");
+      // this lane holds dims 16ks + 2(lane%4) + {0,1} (+8) of head lane/4: the 4 lanes of a quad hold the whole head,
+      // and the RoPE partner d + 64 of every dim sits in the same lane at ks + 4
+      float x[KS][4];
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        x[ks][0] = bf16_lo(qb[ks][0]); x[ks][1] = bf16_hi(qb[ks][0]);
+        x[ks][2] = bf16_lo(qb[ks][1]); x[ks][3] = bf16_hi(qb[ks][1]);
+      }
+      if (p.qnw != nullptr) {
+        float ss = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) ss += x[ks][0] * x[ks][0] + x[ks][1] * x[ks][1] + x[ks][2] * x[ks][2] + x[ks][3] * x[ks][3];
+        ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+        ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+        const float inv = 1.0f / sqrtf(ss / static_cast<float>(D) + p.eps);
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          const int d0 = ks * 16 + (lane & 3) * 2;
+          const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(p.qnw + d0));
+          const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(p.qnw + d0 + 8));
+          x[ks][0] = __bfloat162float(__float2bfloat16_rn(x[ks][0] * inv * bf16_lo(w0)));
+          x[ks][1] = __bfloat162float(__float2bfloat16_rn(x[ks][1] * inv * bf16_hi(w0)));
+          x[ks][2] = __bfloat162float(__float2bfloat16_rn(x[ks][2] * inv * bf16_lo(w1)));
+          x[ks][3] = __bfloat162float(__float2bfloat16_rn(x[ks][3] * inv * bf16_hi(w1)));
+        }
+      }
+      int64_t pos = __ldg(p.pos + b);
+      pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
+      const float* cs = p.cos_sin + pos * D;
+#pragma unroll
+      for (int ks = 0; ks < KS / 2; ++ks) {
+        const int d0 = ks * 16 + (lane & 3) * 2;   // < 64
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int d = d0 + (e & 1) + (e >> 1) * 8;
+          const float c = __ldg(cs + d), sn = __ldg(cs + D / 2 + d);
+          const float x1 = x[ks][e], x2 = x[ks + KS / 2][e];
+          x[ks][e] = x1 * c - x2 * sn;
+          x[ks + KS / 2][e] = x2 * c + x1 * sn;
+        }
+      }
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        qb[ks][0] = hv ? pack_bf16x2(x[ks][0], x[ks][1]) : 0u;
+        qb[ks][1] = hv ? pack_bf16x2(x[ks][2], x[ks][3]) : 0u;
+      }
     }
   }
 
@@ -142,16 +209,8 @@ paged_decode_kernel(const DecodeParams p) {
     cp_async_commit();
   }
 
-  for (int i = 0; i < n; ++i) {
-    cp_async_wait<STAGES - 2>();
-    __syncwarp();
-    if (i + STAGES - 1 < n) issue(i + STAGES - 1);
-    cp_async_commit();
-
-    const int s = i % STAGES;
-    const uint32_t sK = warp_smem + s * C::kStageBytes;
-    const uint32_t sV = sK + C::kSubTileBytes;
-    const int tok_base = ((t0 + i) * NWARPS + warp) * 16;
+  // One 16-token sub-tile of this warp: S^T = K.Q^T, online softmax, O^T += V^T.P^T.  Tokens >= lim are masked.
+  auto process = [&](uint32_t sK, uint32_t sV, int tok_base, int lim) {
     const int mat = lane >> 3;
     const int sw = lane & 7;
 
@@ -173,8 +232,8 @@ paged_decode_kernel(const DecodeParams p) {
     const int tokA = tok_base + (lane >> 2);
     float s0 = sacc[0] * p.scale_log2, s1 = sacc[1] * p.scale_log2;
     float s2 = sacc[2] * p.scale_log2, s3 = sacc[3] * p.scale_log2;
-    if (tokA >= ctx) s0 = s1 = -INFINITY;
-    if (tokA + 8 >= ctx) s2 = s3 = -INFINITY;
+    if (tokA >= lim) s0 = s1 = -INFINITY;
+    if (tokA + 8 >= lim) s2 = s3 = -INFINITY;
     float mx0 = fmaxf(s0, s2), mx1 = fmaxf(s1, s3);
 #pragma unroll
     for (int o = 4; o < 32; o <<= 1) {
@@ -211,6 +270,76 @@ paged_decode_kernel(const DecodeParams p) {
         ldmatrix_x4_trans(a, rowaddr + ((c ^ sw) << 4));
         mma_bf16_16816(acc[mt], a, pb0, pb1);
       }
+    }
+  };
+
+  for (int i = 0; i < n; ++i) {
+    cp_async_wait<STAGES - 2>();
+    __syncwarp();
+    if (i + STAGES - 1 < n) issue(i + STAGES - 1);
+    cp_async_commit();
+    const uint32_t sK = warp_smem + (i % STAGES) * C::kStageBytes;
+    process(sK, sK + C::kSubTileBytes, ((t0 + i) * NWARPS + warp) * 16, ctx);
+  }
+
+  if constexpr (FUSE) {
+    // ---- this step's own token: built here, stored into the cache, attended to from shared memory ----------------
+    const int last_split = tiles_total == 0 ? 0 : (tiles_total - 1) / tps;  // the last split that owns any cached tile
+    if (split == last_split && warp == 0 && ctx_all > 0) {
+      cp_async_wait<0>();
+      __syncwarp();
+      const uint32_t sK = warp_smem, sV = warp_smem + C::kSubTileBytes;
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+      for (int j = 0; j < 2 * C::kSubTileBytes / (32 * 16); ++j)   // zero K and V sub-tiles (rows 1..15 must be finite)
+        *reinterpret_cast<uint4*>(smem + warp * C::kWarpBytes + (j * 32 + lane) * 16) = z;
+      __syncwarp();
+      // lane l owns elements (2l, 2l+1) of each half of the row: exactly the RoPE pairs (j, j + D/2)
+      const bf16* krow = p.q + b * p.q_stride + static_cast<int64_t>(p.H + kvh) * D;
+      const bf16* vrow = p.q + b * p.q_stride + static_cast<int64_t>(p.H + p.Hkv + kvh) * D;
+      const uint32_t ka = *reinterpret_cast<const uint32_t*>(krow + 2 * lane);
+      const uint32_t kb2 = *reinterpret_cast<const uint32_t*>(krow + D / 2 + 2 * lane);
+      const uint32_t va = *reinterpret_cast<const uint32_t*>(vrow + 2 * lane);
+      const uint32_t vb = *reinterpret_cast<const uint32_t*>(vrow + D / 2 + 2 * lane);
+      float x1[2] = {bf16_lo(ka), bf16_hi(ka)}, x2[2] = {bf16_lo(kb2), bf16_hi(kb2)};
+      if (p.knw != nullptr) {
+        float ss = x1[0] * x1[0] + x2[0] * x2[0] + x1[1] * x1[1] + x2[1] * x2[1];
+        ss = warp_sum(ss);
+        const float inv = 1.0f / sqrtf(ss / static_cast<float>(D) + p.eps);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          x1[e] = __bfloat162float(__float2bfloat16_rn(x1[e] * inv * __bfloat162float(p.knw[2 * lane + e])));
+          x2[e] = __bfloat162float(__float2bfloat16_rn(x2[e] * inv * __bfloat162float(p.knw[D / 2 + 2 * lane + e])));
+        }
+      }
+      int64_t pos = __ldg(p.pos + b);
+      pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
+      const float* cs = p.cos_sin + pos * D;
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const float c = __ldg(cs + 2 * lane + e), sn = __ldg(cs + D / 2 + 2 * lane + e);
+        const float o1 = x1[e] * c - x2[e] * sn, o2 = x2[e] * c + x1[e] * sn;
+        x1[e] = o1; x2[e] = o2;
+      }
+      const uint32_t k1 = pack_bf16x2(x1[0], x1[1]), k2 = pack_bf16x2(x2[0], x2[1]);
+      // row 0 of the sub-tile (no swizzle for row 0: chunk c ^ 0)
+      uint32_t* k0s = reinterpret_cast<uint32_t*>(smem + warp * C::kWarpBytes);
+      uint32_t* v0s = reinterpret_cast<uint32_t*>(smem + warp * C::kWarpBytes + C::kSubTileBytes);
+      k0s[lane] = k1; k0s[D / 4 + lane] = k2;
+      v0s[lane] = va; v0s[D / 4 + lane] = vb;
+      if (grp == 0) {
+        const int slot = __ldg(p.slots + b);
+        if (slot >= 0) {
+          const int blk = slot / p.block_size, off = slot - blk * p.block_size;
+          const int64_t o = blk * p.blk_stride + off * p.tok_stride + kvh * p.head_stride;
+          *reinterpret_cast<uint32_t*>(p.kc_w + o + 2 * lane) = k1;
+          *reinterpret_cast<uint32_t*>(p.kc_w + o + D / 2 + 2 * lane) = k2;
+          *reinterpret_cast<uint32_t*>(p.vc_w + o + 2 * lane) = va;
+          *reinterpret_cast<uint32_t*>(p.vc_w + o + D / 2 + 2 * lane) = vb;
+        }
+      }
+      __syncwarp();
+      process(sK, sV, ctx, ctx_all);
     }
   }
 
@@ -305,10 +434,10 @@ __global__ void __launch_bounds__(D) paged_decode_reduce_kernel(const DecodePara
 // ------------------------------------------------------------------------------------------------
 namespace nvllm {
 
-template <int D, int STAGES, int NWARPS>
+template <int D, int STAGES, int NWARPS, bool FUSE = false>
 static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
   using C = DecodeCfg<D, STAGES, NWARPS>;
-  auto kern = paged_decode_kernel<D, STAGES, NWARPS>;
+  auto kern = paged_decode_kernel<D, STAGES, NWARPS, FUSE>;
   NVLLM_SMEM_ATTR_ONCE(kern, C::kSmemBytes);
   dim3 grid(p.num_splits, p.Hkv * p.ngrp, p.batch);
   NVLLM_CUDA(launch_pdl(kern, grid, dim3(NWARPS * 32), C::kSmemBytes, stream, p));
@@ -358,15 +487,23 @@ extern "C" int nvllm_paged_decode_choose_splits(int32_t batch, int32_t num_heads
   return best;
 }
 
-extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache,
-                                            const void* v_cache, const int32_t* block_tables,
-                                            const int32_t* context_lens, int32_t batch,
-                                            int32_t num_heads, int32_t max_blocks_per_seq,
-                                            int64_t q_token_stride, int64_t out_token_stride,
-                                            const nvllm_kv_layout* layout, float scale,
-                                            void* workspace, size_t workspace_bytes,
-                                            int32_t num_splits, int32_t dtype, void* stream) {
-  using namespace nvllm;
+namespace nvllm {
+struct FuseArgs {  // non-NULL positions == fused entry point
+  const int64_t* positions = nullptr;
+  const float* cos_sin = nullptr;
+  const void* q_norm_w = nullptr;
+  const void* k_norm_w = nullptr;
+  const int32_t* slot_mapping = nullptr;
+  float eps = 0.f;
+  int max_position = 0;
+};
+
+static int decode_dispatch(void* out, const void* q, void* k_cache, void* v_cache, const int32_t* block_tables,
+                           const int32_t* context_lens, int32_t batch, int32_t num_heads, int32_t max_blocks_per_seq,
+                           int64_t q_token_stride, int64_t out_token_stride, const nvllm_kv_layout* layout, float scale,
+                           void* workspace, size_t workspace_bytes, int32_t num_splits, int32_t dtype, void* stream,
+                           const FuseArgs& fa) {
+  const bool fuse = fa.positions != nullptr;
   NVLLM_CHECK_ARG(dtype == NVLLM_BF16, NVLLM_ERR_DTYPE, "paged_decode: dtype %d (bf16 only)", dtype);
   if (int rc = check_layout(layout)) return rc;
   NVLLM_CHECK_ARG(batch >= 0 && batch <= 65535, NVLLM_ERR_ARG, "paged_decode: batch %d", batch);
@@ -382,10 +519,15 @@ extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void
                   "paged_decode: NULL pointer");
   NVLLM_CHECK_ARG(aligned16(out) && aligned16(q) && aligned16(k_cache) && aligned16(v_cache),
                   NVLLM_ERR_ALIGN, "paged_decode: pointers must be 16-byte aligned");
-  NVLLM_CHECK_ARG(q_token_stride % 8 == 0 && out_token_stride % 8 == 0 &&
-                      q_token_stride >= static_cast<int64_t>(num_heads) * D &&
+  const int64_t q_row = fuse ? static_cast<int64_t>(num_heads + 2 * Hkv) * D : static_cast<int64_t>(num_heads) * D;
+  NVLLM_CHECK_ARG(q_token_stride % 8 == 0 && out_token_stride % 8 == 0 && q_token_stride >= q_row &&
                       out_token_stride >= static_cast<int64_t>(num_heads) * D,
                   NVLLM_ERR_ALIGN, "paged_decode: q/out token stride");
+  if (fuse) {
+    NVLLM_CHECK_ARG(D == 128, NVLLM_ERR_ARG, "paged_decode_fused: head_dim %d (128 only)", D);
+    NVLLM_CHECK_ARG(fa.cos_sin && fa.slot_mapping && fa.max_position > 0 && (fa.q_norm_w == nullptr) == (fa.k_norm_w == nullptr),
+                    NVLLM_ERR_ARG, "paged_decode_fused: cos_sin / slot_mapping / norm weights");
+  }
   const int g = num_heads / Hkv;
   if (num_splits <= 0)
     num_splits = nvllm_paged_decode_choose_splits(batch, num_heads, Hkv,
@@ -396,6 +538,15 @@ extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void
   p.q = static_cast<const bf16*>(q);
   p.kc = static_cast<const bf16*>(k_cache);
   p.vc = static_cast<const bf16*>(v_cache);
+  p.kc_w = static_cast<bf16*>(k_cache);
+  p.vc_w = static_cast<bf16*>(v_cache);
+  p.qnw = static_cast<const bf16*>(fa.q_norm_w);
+  p.knw = static_cast<const bf16*>(fa.k_norm_w);
+  p.cos_sin = fa.cos_sin;
+  p.pos = fa.positions;
+  p.slots = fa.slot_mapping;
+  p.eps = fa.eps;
+  p.max_position = fa.max_position;
   p.tables = block_tables;
   p.ctx = context_lens;
   p.ws_o = nullptr;
@@ -424,6 +575,7 @@ extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void
   p.head_stride = layout->head_stride;
   p.scale_log2 = scale * 1.4426950408889634f;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (fuse) return launch_decode<128, 3, 4, true>(p, st);
   if (D == 128) {
     switch (decode_cfg_id()) {
       case 1: return launch_decode<128, 4, 4>(p, st);
@@ -434,4 +586,35 @@ extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void
     }
   }
   return launch_decode<64, 4, 4>(p, st);
+}
+}  // namespace nvllm
+
+extern "C" int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache,
+                                            const void* v_cache, const int32_t* block_tables,
+                                            const int32_t* context_lens, int32_t batch,
+                                            int32_t num_heads, int32_t max_blocks_per_seq,
+                                            int64_t q_token_stride, int64_t out_token_stride,
+                                            const nvllm_kv_layout* layout, float scale,
+                                            void* workspace, size_t workspace_bytes,
+                                            int32_t num_splits, int32_t dtype, void* stream) {
+  return nvllm::decode_dispatch(out, q, const_cast<void*>(k_cache), const_cast<void*>(v_cache), block_tables, context_lens,
+                                batch, num_heads, max_blocks_per_seq, q_token_stride, out_token_stride, layout, scale, workspace,
+                                workspace_bytes, num_splits, dtype, stream, nvllm::FuseArgs{});
+}
+
+extern "C" int nvllm_paged_decode_attention_fused(void* out, const void* qkv, const int64_t* positions, const float* cos_sin,
+                                                  const void* q_norm_w, const void* k_norm_w, float eps, int32_t max_position,
+                                                  void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                                                  const int32_t* block_tables, const int32_t* context_lens, int32_t batch,
+                                                  int32_t num_heads, int32_t max_blocks_per_seq, int64_t qkv_token_stride,
+                                                  int64_t out_token_stride, const nvllm_kv_layout* layout, float scale,
+                                                  void* workspace, size_t workspace_bytes, int32_t num_splits, int32_t dtype,
+                                                  void* stream) {
+  NVLLM_CHECK_ARG(positions != nullptr, NVLLM_ERR_ARG, "paged_decode_fused: positions is NULL");
+  nvllm::FuseArgs fa;
+  fa.positions = positions; fa.cos_sin = cos_sin; fa.q_norm_w = q_norm_w; fa.k_norm_w = k_norm_w;
+  fa.slot_mapping = slot_mapping; fa.eps = eps; fa.max_position = max_position;
+  return nvllm::decode_dispatch(out, qkv, k_cache, v_cache, block_tables, context_lens, batch, num_heads, max_blocks_per_seq,
+                                qkv_token_stride, out_token_stride, layout, scale, workspace, workspace_bytes, num_splits, dtype,
+                                stream, fa);
 }

@@ -64,6 +64,33 @@ def paged_decode_attention(q, k_cache, v_cache, block_tables, context_lens, layo
     return out
 
 
+def paged_decode_attention_fused(qkv, positions, cos_sin, q_norm_w, k_norm_w, eps, k_cache, v_cache, slot_mapping, block_tables,
+                                 context_lens, num_heads, layout: KvLayout, scale=None, num_splits=0, out=None, workspace=None):
+    """q/k-norm + RoPE + store_kv_cache + flash_attention_decode in one launch (qwen3.rs:219-233).  qkv: [B, (H+2Hkv)*D]
+    packed rows of this step (read only); context_lens counts this step's token.  -> out [B, H, D]."""
+    _need(qkv, torch.bfloat16, "qkv"); _need(positions, torch.int64, "positions"); _need(cos_sin, torch.float32, "cos_sin")
+    _need(block_tables, torch.int32, "block_tables"); _need(context_lens, torch.int32, "context_lens")
+    _need(slot_mapping, torch.int32, "slot_mapping")
+    B, H, D = qkv.shape[0], num_heads, layout.head_dim
+    assert qkv.is_contiguous() and qkv.shape[1] == (H + 2 * layout.num_kv_heads) * D and block_tables.is_contiguous()
+    if out is None:
+        out = torch.empty((B, H, D), dtype=torch.bfloat16, device=qkv.device)
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    if num_splits == 0:
+        num_splits = _ffi.lib().nvllm_paged_decode_choose_splits(B, H, layout.num_kv_heads,
+                                                                 block_tables.shape[1] * layout.block_size)
+    need = paged_decode_workspace_bytes(B, H, D, num_splits)
+    if need and (workspace is None or workspace.numel() * workspace.element_size() < need):
+        workspace = torch.empty(need, dtype=torch.uint8, device=qkv.device)
+    check(_ffi.lib().nvllm_paged_decode_attention_fused(
+        _p(out), _p(qkv), _p(positions), _p(cos_sin), _p(q_norm_w), _p(k_norm_w), eps, cos_sin.shape[0], _p(k_cache),
+        _p(v_cache), _p(slot_mapping), _p(block_tables), _p(context_lens), B, H, block_tables.shape[1], qkv.stride(0),
+        out.stride(0), layout, scale, _p(workspace),
+        0 if workspace is None else workspace.numel() * workspace.element_size(), num_splits, BF16, _stream()))
+    return out
+
+
 def varlen_prefill_attention(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, scale=None,
                              k_cache=None, v_cache=None, block_tables=None, layout: KvLayout = None, out=None):
     """Attention::flash_attention_varlen / _with_cache (attention.rs:177-222). q: [N, H, D]; k, v: [Nk, Hkv, D]."""

@@ -77,6 +77,67 @@ def test_paged_decode_attention_vs_oracle(cuda, kind, case):
     assert_close(to_np_f32(out), ref, ATT_ATOL, ATT_RTOL, f"paged decode {case}")
 
 
+FUSED_CASES = [
+    # (context_lens INCLUDING this step's token, H, Hkv, block_size, num_splits, qk_norm)
+    ([1], 16, 8, 256, 1, True),                             # nothing cached: the step's own token only
+    ([6, 301, 257, 258, 1025, 18, 513], 16, 8, 256, 1, True),  # Qwen3-0.6B heads; new token opens a block (257, 513, 1025)
+    ([6, 301, 257, 258, 1025, 18, 513], 16, 8, 256, 3, True),  # through split-K: the last non-empty split owns the new token
+    ([701, 65, 2, 17], 32, 8, 256, 0, True),                # Qwen3-8B group 4, library-chosen splits
+    ([2001, 34], 8, 1, 256, 4, True),                       # TP=8 shard of Qwen3-32B: 1 kv head, group 8
+    ([130, 48, 17, 16], 4, 2, 16, 2, True),                 # block size 16: new token first / last in its block
+    ([91, 201], 12, 1, 32, 1, False),                       # group 12 > 8 (two q-head groups, one stores), no qk-norm
+    ([0, 41], 16, 8, 256, 1, True),                         # padded graph row: ctx 0, slot -1 -> zeros, nothing stored
+]
+
+
+@pytest.mark.parametrize("kind", ["reference", "head_major"])
+@pytest.mark.parametrize("case", FUSED_CASES, ids=[str(i) for i in range(len(FUSED_CASES))])
+def test_paged_decode_attention_fused_vs_oracle(cuda, kind, case):
+    """nvllm_paged_decode_attention_fused = q/k-norm + RoPE + store_kv_cache + paged decode attention in one launch, against
+    the oracle's three functions in sequence.  Attention output within the attention tolerance; the stored K row within the
+    RoPE tolerance (2 bf16 ulps), the stored V row and every other cache byte bit-exact."""
+    from nano_vllm_rs_b200 import ops
+    ctx, H, Hkv, bs, splits, qknorm = case
+    D, B, maxpos = 128, len(ctx), 4096
+    rng = np.random.default_rng(B * 977 + H + bs)
+    cached = [max(c - 1, 0) for c in ctx]
+    kc, vc, tables, _, _ = make_paged_kv(rng, [c + 1 for c in cached], bs, Hkv, D)   # room for the new token's block
+    # the slot of the new token must hold garbage before the call (make_paged_kv wrote c+1 tokens): scrub it to a marker
+    qkv = randn_bf16(rng, (B, (H + 2 * Hkv) * D))
+    pos = np.asarray([max(c - 1, 0) for c in ctx], np.int64)
+    slots = np.asarray([(tables[b, cached[b] // bs] * bs + cached[b] % bs) if ctx[b] > 0 else -1 for b in range(B)], np.int32)
+    qw = round_bf16(1.0 + 0.1 * rng.standard_normal(D).astype(np.float32)) if qknorm else None
+    kw = round_bf16(1.0 + 0.1 * rng.standard_normal(D).astype(np.float32)) if qknorm else None
+    table = O.rope_cos_sin_table(maxpos, D, 1e6)
+    scale = 1.0 / np.sqrt(D)
+    # ---- oracle: qknorm_rope -> store_kv_cache -> flash_attention_decode
+    q = qkv[:, : H * D].reshape(B, H, D); k = qkv[:, H * D : (H + Hkv) * D].reshape(B, Hkv, D)
+    v = qkv[:, (H + Hkv) * D :].reshape(B, Hkv, D)
+    q_ref, k_ref = O.qknorm_rope(q, k, pos, table, qw, kw, 1e-6)
+    kc_ref, vc_ref = kc.copy(), vc.copy()
+    O.store_kv_cache(k_ref, v, kc_ref, vc_ref, slots)
+    ref = O.flash_attention_decode(q_ref, kc_ref, vc_ref, tables, np.asarray(ctx, np.int32), scale)
+    # ---- device
+    kd, vd = cache_to_layout(kc, kind, cuda), cache_to_layout(vc, kind, cuda)
+    qkv_d = to_dev_bf16(qkv, cuda)
+    out = ops.paged_decode_attention_fused(
+        qkv_d, torch.from_numpy(pos).to(cuda), torch.from_numpy(table).to(cuda), None if qw is None else to_dev_bf16(qw, cuda),
+        None if kw is None else to_dev_bf16(kw, cuda), 1e-6, kd, vd, torch.from_numpy(slots).to(cuda),
+        torch.from_numpy(tables).to(cuda), torch.tensor(ctx, dtype=torch.int32, device=cuda), H, _layout(kind, bs, Hkv, D),
+        scale=scale, num_splits=splits)
+    torch.cuda.synchronize()
+    assert np.array_equal(to_np_f32(qkv_d), qkv), "the packed qkv rows are read only"
+    assert_close(to_np_f32(out), ref, ATT_ATOL, ATT_RTOL, f"fused paged decode {case}")
+    kc_got, vc_got = cache_from_layout(kd, kind), cache_from_layout(vd, kind)
+    assert np.array_equal(vc_got, vc_ref), "V rows are copied bit-exactly, nothing else in the cache may change"
+    mask = np.zeros(kc.shape[:2], bool)
+    for b in range(B):
+        if slots[b] >= 0:
+            mask[slots[b] // bs, slots[b] % bs] = True
+    assert np.array_equal(kc_got[~mask], kc[~mask]), "only the new tokens' slots may change"
+    assert_close(kc_got[mask], kc_ref[mask], 2e-3, 2 ** -6, "stored K rows (norm + RoPE)")
+
+
 def test_paged_decode_full_size_properties(cuda):
     """BASELINE config 2 shape (256 seqs x 1024 ctx, 16/8 heads): size-independent checks —
     (i) V == const c per head  =>  out == c exactly representable in bf16;  (ii) split-K invariance;
