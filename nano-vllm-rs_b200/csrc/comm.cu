@@ -7,6 +7,8 @@
 #include <dlfcn.h>
 #include <string.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace nvllm {
@@ -65,14 +67,18 @@ static int nccl_status(int rc, const char* what) {
 
 }  // namespace nvllm
 
-// Symmetric region: [control block 4 KiB | user data].  Control block (all uint32; the first two arrays are written
-// remotely by peers):  ready[8] at +0, done[8] at +256, then local-only: CTA counter at +512, epoch at +516, dead at +520.
+// Symmetric region: [control block 4 KiB | low-latency area: 3 x (stage, bcast) of ll_cap bytes | user data].
+// Control block (all uint32; the first two arrays are written remotely by peers):  ready[8] at +0, done[8] at +256, then
+// local-only: CTA counter at +512, epoch at +516, dead at +520, low-latency buffer index at +524, bytes in use of each
+// low-latency buffer at +528..+539, low-latency CTA counter at +540.
 struct nvllm_comm {
   nvllm::ncclComm_t comm = nullptr;
   int rank = 0, world = 1;
   uint8_t* sym_local = nullptr;       // this rank's region (cudaMalloc)
   uint8_t* sym_peer[8] = {nullptr};   // every rank's region as mapped into this process (own entry == sym_local)
   size_t sym_bytes = 0;
+  size_t ll_cap = 0;                  // bytes of ONE low-latency buffer (6 of them sit between the control block and user data)
+  size_t user_off = 0;                // offset of the user data inside the region
   int* h_err = nullptr;               // pinned + mapped: a fused kernel that gave up waiting for a peer sets it
   int* d_err = nullptr;               // device alias of h_err
 };
@@ -260,6 +266,274 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Low-latency variant for decode-sized messages: same arithmetic (bit for bit, up to the sign of zero), no flags.
+//
+// The flag protocol above costs two system-scope barriers per call (flag store -> peer poll, ~2-3 us each), a pull over
+// NVLink (a full round trip) and a system fence that waits for every remote write to be acknowledged: ~17 us per call at
+// 2 ranks however small the message.  Here the DATA is the signal: every 32-bit word of a buffer that has not been written
+// yet holds kLLEmpty (two bf16 -0.0), senders replace that one bit pattern by +0.0 (numerically the same value), and a
+// receiver spins on the 16-byte vector itself until none of its four words is kLLEmpty.  One NVLink one-way trip per shot:
+//   A  push   every rank stores its partial rows straight into the OWNER's stage buffer   stage[src rank][row][hidden]
+//   B  reduce the owner polls the world-1 staged copies of a vector (its own partial is local), adds in rank order, rounds,
+//             adds the residual, normalises, stores the normed row locally and pushes it into every peer's bcast buffer
+//   C  gather every rank polls the rows it does not own in its bcast buffer and copies them to `out`
+// Three (stage, bcast) pairs rotate per call; a call clears the pair two calls ahead.  Why that is race-free: a peer can
+// be at most ONE call ahead of this rank (to finish call i+1 it needs this rank's partial rows of call i+1), so during
+// call i nothing can arrive for pair (i+2) % 3; everything that was ever pushed into that pair during call i-1 has been
+// polled (every vector, phases B and C), so nothing can land late either; and the clear completes with this kernel,
+// before this rank enters call i+1.  x / residual / out are ordinary local buffers for this kernel.
+// Every CTA waits for remote CTAs that may not have started: the grid must be co-resident (launch_fused_ar_ll sizes it
+// from the occupancy calculator), and phase A comes first in every CTA, unconditionally.
+constexpr uint32_t kLLEmpty = 0x80008000u;
+
+__device__ __forceinline__ void st_sys_16(void* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ll_scrub(uint4 v) {
+  v.x = v.x == kLLEmpty ? 0u : v.x;
+  v.y = v.y == kLLEmpty ? 0u : v.y;
+  v.z = v.z == kLLEmpty ? 0u : v.z;
+  v.w = v.w == kLLEmpty ? 0u : v.w;
+  return v;
+}
+__device__ __forceinline__ bool ll_arrived(const uint4& v) {
+  return v.x != kLLEmpty && v.y != kLLEmpty && v.z != kLLEmpty && v.w != kLLEmpty;
+}
+// Re-polls one vector until it has arrived (slow path of the batched first attempt); same give-up rule as wait_flag.
+__device__ __noinline__ uint4 ll_spin(const void* p, long long timeout_cycles, uint32_t* dead, int* err) {
+  const long long t0 = clock64();
+  uint4 v = ld_sys_16(p);
+  while (!ll_arrived(v)) {
+    if (clock64() - t0 > timeout_cycles || *reinterpret_cast<volatile uint32_t*>(dead) != 0) {
+      *reinterpret_cast<volatile uint32_t*>(dead) = 1u;
+      *reinterpret_cast<volatile int*>(err) = 1;
+      __threadfence_system();
+      break;
+    }
+    v = ld_sys_16(p);
+  }
+  return v;
+}
+
+struct LLArParams {
+  uint8_t* peer[8];          // symmetric regions of all ranks as mapped here
+  uint8_t* self;
+  const uint8_t* x;          // this rank's partial sums [num_tokens, hidden] (local)
+  uint8_t* res;              // residual, row-sharded: only this rank's rows are read / written
+  uint8_t* out;              // normed rows, all of them (local)
+  const bf16* weight;
+  size_t ll_off, ll_cap;     // low-latency area inside a region; bytes of one buffer
+  int rank, num_tokens, hidden;
+  float eps;
+  long long timeout_cycles;
+  int* err;
+};
+__device__ __forceinline__ uint8_t* peer_of(const LLArParams& p, unsigned q) {
+  uint8_t* r = p.peer[0];
+#pragma unroll
+  for (unsigned i = 1; i < 8; ++i) r = (q == i) ? p.peer[i] : r;
+  return r;
+}
+
+template <int WORLD, int VPT>
+__global__ void __launch_bounds__(512)
+allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
+  uint32_t* ctrl = reinterpret_cast<uint32_t*>(p.self);
+  const uint32_t b = ctrl[131];                          // pair of this call; advanced by the last CTA of the call
+  const uint32_t bclr = b >= 1 ? b - 1 : 2;              // (b + 2) % 3
+  const uint32_t clr_bytes = ctrl[132 + bclr];           // what the last call on that pair used
+  uint32_t* dead_p = ctrl + 130;
+  const bool dead = *dead_p != 0;
+  const int R = (p.num_tokens + WORLD - 1) / WORLD;      // rows per owner
+  const size_t row_bytes = static_cast<size_t>(p.hidden) * 2;
+  const size_t stage_off = p.ll_off + static_cast<size_t>(b) * 2 * p.ll_cap;
+  const size_t bcast_off = stage_off + p.ll_cap;
+  const int nvec = p.hidden >> 3;
+
+  // ---- A: push my partial rows to their owners -------------------------------------------------------------------
+  for (int row = blockIdx.x; row < p.num_tokens; row += gridDim.x) {
+    const int owner = row / R;
+    if (owner == p.rank) continue;
+    const uint8_t* src = p.x + row * row_bytes;
+    uint8_t* dst = peer_of(p, owner) + stage_off + (static_cast<size_t>(p.rank) * R + (row - owner * R)) * row_bytes;
+    uint4 v[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int i = threadIdx.x + k * blockDim.x;
+      if (i < nvec) v[k] = *reinterpret_cast<const uint4*>(src + i * 16);
+    }
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int i = threadIdx.x + k * blockDim.x;
+      if (i < nvec) st_sys_16(dst + i * 16, ll_scrub(v[k]));
+    }
+  }
+  // ---- housekeeping while the pushes fly: clear the pair two calls ahead ------------------------------------------
+  {
+    uint4* c0 = reinterpret_cast<uint4*>(p.self + p.ll_off + static_cast<size_t>(bclr) * 2 * p.ll_cap);
+    uint4* c1 = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(c0) + p.ll_cap);
+    const uint4 e = make_uint4(kLLEmpty, kLLEmpty, kLLEmpty, kLLEmpty);
+    const uint32_t n16 = clr_bytes >> 4;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) { c0[i] = e; c1[i] = e; }
+  }
+  // ---- B: reduce + add + norm the rows I own, broadcast them -----------------------------------------------------
+  const int row0 = p.rank * R;
+  const int row1 = min(p.num_tokens, row0 + R);
+  const uint4* wv = reinterpret_cast<const uint4*>(p.weight);
+  constexpr int KCH = VPT < 2 ? VPT : 2;
+  __shared__ float red[16];
+  __shared__ float s_inv;
+  for (int row = row0 + blockIdx.x; row < row1; row += gridDim.x) {
+    const size_t roff = row * row_bytes;
+    const uint8_t* st_row = p.self + stage_off + static_cast<size_t>(row - row0) * row_bytes;  // + q * R * row_bytes
+    uint32_t sw[VPT][4];
+    float ss = 0.f;
+#pragma unroll
+    for (int k0 = 0; k0 < VPT; k0 += KCH) {
+      uint4 a[KCH][WORLD], r[KCH];
+#pragma unroll
+      for (int k = 0; k < KCH; ++k) {
+        const int i = threadIdx.x + (k0 + k) * blockDim.x;
+        if (i < nvec) {
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q)
+            a[k][q] = (q == p.rank) ? *reinterpret_cast<const uint4*>(p.x + roff + i * 16)
+                                    : ld_sys_16(st_row + static_cast<size_t>(q) * R * row_bytes + i * 16);
+          r[k] = *reinterpret_cast<const uint4*>(p.res + roff + i * 16);
+        }
+      }
+      if (!dead) {
+#pragma unroll
+        for (int k = 0; k < KCH; ++k) {
+          const int i = threadIdx.x + (k0 + k) * blockDim.x;
+          if (i < nvec) {
+#pragma unroll
+            for (int q = 0; q < WORLD; ++q)
+              if (q != p.rank && !ll_arrived(a[k][q]))
+                a[k][q] = ll_spin(st_row + static_cast<size_t>(q) * R * row_bytes + i * 16, p.timeout_cycles, dead_p, p.err);
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < KCH; ++k) {
+        const int i = threadIdx.x + (k0 + k) * blockDim.x;
+        if (i < nvec) {
+          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int q = 0; q < WORLD; ++q) {  // fixed order: identical bits whichever rank owns the row
+            const uint32_t aw[4] = {a[k][q].x, a[k][q].y, a[k][q].z, a[k][q].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(aw[j]); acc[2 * j + 1] += bf16_hi(aw[j]); }
+          }
+          const uint32_t rw[4] = {r[k].x, r[k].y, r[k].z, r[k].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t o = pack_bf16x2(acc[2 * j], acc[2 * j + 1]);
+            const uint32_t h = pack_bf16x2(bf16_lo(o) + bf16_lo(rw[j]), bf16_hi(o) + bf16_hi(rw[j]));
+            sw[k0 + k][j] = h;
+            const float v0 = bf16_lo(h), v1 = bf16_hi(h);
+            ss += v0 * v0 + v1 * v1;
+          }
+        }
+      }
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      float t = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.f;
+      t = warp_sum(t);
+      if (threadIdx.x == 0) s_inv = 1.0f / sqrtf(t / static_cast<float>(p.hidden) + p.eps);
+    }
+    __syncthreads();
+    const float inv = s_inv;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int i = threadIdx.x + k * blockDim.x;
+      if (i < nvec) {
+        const uint4 w = __ldg(wv + i);
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+        uint4 o;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          ow[j] = pack_bf16x2(bf16_lo(sw[k][j]) * inv * bf16_lo(ww[j]), bf16_hi(sw[k][j]) * inv * bf16_hi(ww[j]));
+        o = ll_scrub(o);  // the same bits on the owner and on the receivers
+#pragma unroll
+        for (int q = 0; q < WORLD; ++q)
+          if (q != p.rank) st_sys_16(p.peer[q] + bcast_off + roff + i * 16, o);
+        *reinterpret_cast<uint4*>(p.res + roff + i * 16) = make_uint4(sw[k][0], sw[k][1], sw[k][2], sw[k][3]);
+        *reinterpret_cast<uint4*>(p.out + roff + i * 16) = o;
+      }
+    }
+    __syncthreads();  // red / s_inv reuse
+  }
+  // ---- C: gather the rows the other ranks own ----------------------------------------------------------------------
+  for (int row = blockIdx.x; row < p.num_tokens; row += gridDim.x) {
+    if (row / R == p.rank) continue;
+    const uint8_t* src = p.self + bcast_off + row * row_bytes;
+    uint4 v[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int i = threadIdx.x + k * blockDim.x;
+      if (i < nvec) v[k] = ld_sys_16(src + i * 16);
+    }
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int i = threadIdx.x + k * blockDim.x;
+      if (i < nvec) {
+        if (!dead && !ll_arrived(v[k])) v[k] = ll_spin(src + i * 16, p.timeout_cycles, dead_p, p.err);
+        *reinterpret_cast<uint4*>(p.out + row * row_bytes + i * 16) = v[k];
+      }
+    }
+  }
+  // ---- the last CTA rotates the pair -------------------------------------------------------------------------------
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(ctrl + 135, 1u) == gridDim.x - 1) {
+      ctrl[135] = 0;
+      ctrl[132 + b] = static_cast<uint32_t>(static_cast<size_t>(WORLD) * R * row_bytes);
+      ctrl[131] = b == 2 ? 0u : b + 1;
+      __threadfence();
+    }
+  }
+}
+
+template <int WORLD, int VPT>
+static int launch_fused_ar_ll_v(const LLArParams& p, int threads, cudaStream_t st) {
+  static std::atomic<int> per_sm_of[17];  // co-residency bound of this instantiation, by block size / 32
+  int per_sm = per_sm_of[threads / 32].load(std::memory_order_relaxed);
+  if (per_sm == 0) {
+    int n = 0;
+    NVLLM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, allreduce_add_rmsnorm_ll_kernel<WORLD, VPT>, threads, 0));
+    per_sm = n < 1 ? 1 : n;
+    per_sm_of[threads / 32].store(per_sm, std::memory_order_relaxed);
+  }
+  if (per_sm > 2) per_sm = 2;  // leaves room for the PDL successor's prologue; two rows per SM in flight are plenty
+  int grid = p.num_tokens < per_sm * sm_count() ? p.num_tokens : per_sm * sm_count();
+  NVLLM_CUDA(launch_pdl(allreduce_add_rmsnorm_ll_kernel<WORLD, VPT>, dim3(grid), dim3(threads), 0, st, p));
+  return 0;
+}
+template <int WORLD>
+static int launch_fused_ar_ll(const LLArParams& p, cudaStream_t st) {
+  const int nvec = p.hidden / 8;
+  const int vpt = nvec <= 128 ? 1 : (nvec <= 1024 ? 2 : 4);
+  int threads = ((nvec + vpt - 1) / vpt + 31) / 32 * 32;
+  if (threads < 32) threads = 32;
+  if (vpt == 1) return launch_fused_ar_ll_v<WORLD, 1>(p, threads, st);
+  if (vpt == 2) return launch_fused_ar_ll_v<WORLD, 2>(p, threads, st);
+  return launch_fused_ar_ll_v<WORLD, 4>(p, threads, st);
+}
+
+__global__ void ll_fill_kernel(uint4* p, size_t n16) {
+  const uint4 e = make_uint4(kLLEmpty, kLLEmpty, kLLEmpty, kLLEmpty);
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n16; i += static_cast<size_t>(gridDim.x) * blockDim.x) p[i] = e;
+}
+
 template <int WORLD>
 static int launch_fused_ar(const FusedArParams& p, int rows_per, cudaStream_t st) {
   const int nvec = p.hidden / 8;
@@ -312,10 +586,17 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base) {
   NVLLM_CHECK_ARG(comm && comm->comm && local_base && bytes > 0, NVLLM_ERR_ARG, "comm_symm_alloc: arguments");
   NVLLM_CHECK_ARG(comm->sym_local == nullptr, NVLLM_ERR_STATE, "comm_symm_alloc: already allocated");
   NVLLM_CHECK_ARG(comm->world <= 8, NVLLM_ERR_ARG, "comm_symm_alloc: world %d > 8", comm->world);
-  const size_t total = kSymCtrlBytes + ((bytes + 255) & ~static_cast<size_t>(255));
+  const size_t ll_cap = (static_cast<size_t>(knobs().ar_ll_max_bytes) + 255) & ~static_cast<size_t>(255);
+  const size_t user_off = kSymCtrlBytes + 6 * ll_cap;
+  const size_t total = user_off + ((bytes + 255) & ~static_cast<size_t>(255));
   void* base = nullptr;
   NVLLM_CUDA(cudaMalloc(&base, total));
   NVLLM_CUDA(cudaMemset(base, 0, total));
+  if (ll_cap > 0) {  // "nothing has arrived" everywhere, before any peer can learn this region's handle
+    ll_fill_kernel<<<256, 256>>>(reinterpret_cast<uint4*>(static_cast<uint8_t*>(base) + kSymCtrlBytes), 6 * ll_cap / 16);
+    NVLLM_CUDA(cudaGetLastError());
+    NVLLM_CUDA(cudaDeviceSynchronize());
+  }
   cudaIpcMemHandle_t mine;
   NVLLM_CUDA(cudaIpcGetMemHandle(&mine, base));
   cudaIpcMemHandle_t* d_all = nullptr;
@@ -348,7 +629,9 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base) {
   }
   comm->sym_local = static_cast<uint8_t*>(base);
   comm->sym_bytes = total;
-  *local_base = comm->sym_local + kSymCtrlBytes;
+  comm->ll_cap = ll_cap;
+  comm->user_off = user_off;
+  *local_base = comm->sym_local + user_off;
   return 0;
 }
 
@@ -359,9 +642,31 @@ int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* resi
   NVLLM_CHECK_ARG(dtype == NVLLM_BF16, NVLLM_ERR_DTYPE, "allreduce_add_rmsnorm: dtype %d", dtype);
   NVLLM_CHECK_ARG(num_tokens >= 0 && hidden > 0 && hidden % 8 == 0 && hidden <= 16384, NVLLM_ERR_ARG, "allreduce_add_rmsnorm: sizes");
   if (num_tokens == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int rows_per = (num_tokens + comm->world - 1) / comm->world;
+  const size_t staged = static_cast<size_t>(comm->world) * rows_per * hidden * 2;
+  if (knobs().ar_ll && staged <= comm->ll_cap && (comm->world == 2 || comm->world == 4 || comm->world == 8)) {
+    NVLLM_CHECK_ARG(out && x && residual && weight && ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(x) |
+                                                         reinterpret_cast<uintptr_t>(residual)) & 15) == 0,
+                    NVLLM_ERR_ARG, "allreduce_add_rmsnorm: out / x / residual must be 16-byte aligned");
+    LLArParams q;
+    for (int r = 0; r < 8; ++r) q.peer[r] = r < comm->world ? comm->sym_peer[r] : nullptr;
+    q.self = comm->sym_local;
+    q.x = static_cast<const uint8_t*>(x); q.res = static_cast<uint8_t*>(residual); q.out = static_cast<uint8_t*>(out);
+    q.weight = static_cast<const bf16*>(weight);
+    q.ll_off = kSymCtrlBytes; q.ll_cap = comm->ll_cap;
+    q.rank = comm->rank; q.num_tokens = num_tokens; q.hidden = hidden; q.eps = eps;
+    q.timeout_cycles = knobs().comm_timeout_ms * 2000000ll;
+    q.err = comm->d_err;
+    switch (comm->world) {
+      case 2: return launch_fused_ar_ll<2>(q, st);
+      case 4: return launch_fused_ar_ll<4>(q, st);
+      default: return launch_fused_ar_ll<8>(q, st);
+    }
+  }
   auto off = [&](const void* ptr, size_t* o) {
     const uint8_t* b = static_cast<const uint8_t*>(ptr);
-    if (b < comm->sym_local + kSymCtrlBytes || b + static_cast<size_t>(num_tokens) * hidden * 2 > comm->sym_local + comm->sym_bytes) return false;
+    if (b < comm->sym_local + comm->user_off || b + static_cast<size_t>(num_tokens) * hidden * 2 > comm->sym_local + comm->sym_bytes) return false;
     *o = static_cast<size_t>(b - comm->sym_local);
     return (*o & 15) == 0;
   };
@@ -374,8 +679,6 @@ int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* resi
   p.rank = comm->rank; p.num_tokens = num_tokens; p.hidden = hidden; p.eps = eps;
   p.timeout_cycles = knobs().comm_timeout_ms * 2000000ll;  // clock64 ticks at <= 2 GHz
   p.err = comm->d_err;
-  const int rows_per = (num_tokens + comm->world - 1) / comm->world;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (comm->world) {
     case 2: return launch_fused_ar<2>(p, rows_per, st);
     case 4: return launch_fused_ar<4>(p, rows_per, st);

@@ -63,6 +63,8 @@ struct Knobs {
   int fuse_rope = 0;        // NVLLM_FUSE_ROPE: qkv GEMM epilogue with q/k-norm + RoPE + KV store
   int fuse_decode = 1;      // NVLLM_FUSE_DECODE: 0 = separate qknorm_rope_store launch before the paged decode attention
   int fused_tp = 1;         // NVLLM_FUSED_TP: 0 = ncclAllReduce + separate add_rmsnorm
+  int ar_ll = 1;            // NVLLM_AR_LL: 0 = always the flag-protocol fused all-reduce (no low-latency push variant)
+  long long ar_ll_max_bytes = 8ll << 20;  // NVLLM_AR_LL_MAX_BYTES: largest message of the low-latency variant (6x this is reserved)
   int profile = 0;          // NVLLM_PROFILE: 1 = the runner times every launch of eager steps with CUDA events
   long long comm_timeout_ms = 600000;  // NVLLM_COMM_TIMEOUT_MS: peer-flag spin bound of the fused TP kernels
 };
