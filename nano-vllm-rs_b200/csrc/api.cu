@@ -50,7 +50,7 @@ static void parse_knobs() {
   k.decode_cfg = num("NVLLM_DECODE_CFG", 0);
   k.prefill_poly = num("NVLLM_PREFILL_POLY", 4);
   k.fuse_rope = num("NVLLM_FUSE_ROPE", 0) == 1;
-  k.fuse_decode = num("NVLLM_FUSE_DECODE", 1);
+  k.fuse_decode = num("NVLLM_FUSE_DECODE", 0);
   k.fused_tp = num("NVLLM_FUSED_TP", 1);
   k.profile = num("NVLLM_PROFILE", 0);
   k.ar_ll = num("NVLLM_AR_LL", 1);

@@ -104,6 +104,43 @@ paged_decode_kernel(const DecodeParams p) {
   const int t1 = min(t0 + tps, tiles_total);
   const int n = max(t1 - t0, 0);
 
+  const uint32_t warp_smem = smem_u32(smem) + warp * C::kWarpBytes;
+  const int32_t* table = p.tables + static_cast<int64_t>(b) * p.max_blocks;
+  const bf16* kbase = p.kc + kvh * p.head_stride;
+  const bf16* vbase = p.vc + kvh * p.head_stride;
+
+  auto issue = [&](int i) {
+    const int s = i % STAGES;
+    const int tok_base = ((t0 + i) * NWARPS + warp) * 16;
+    int blk = -1, off = 0;
+    if (tok_base < ctx) {
+      const int bi = tok_base / p.block_size;
+      off = tok_base - bi * p.block_size;
+      if (bi < p.max_blocks) blk = __ldg(table + bi);
+    }
+    const uint32_t sK = warp_smem + s * C::kStageBytes;
+    const uint32_t sV = sK + C::kSubTileBytes;
+    const int c = lane % C::kChunks;
+    const int r0 = lane / C::kChunks;
+    const int64_t gofs0 = static_cast<int64_t>(blk < 0 ? 0 : blk) * p.blk_stride + c * 8;
+#pragma unroll
+    for (int j = 0; j < C::kRowsPerLane; ++j) {
+      const int r = r0 + j * C::kRowStep;
+      const bool valid = (blk >= 0) && (tok_base + r < ctx);
+      const int64_t gofs = valid ? gofs0 + static_cast<int64_t>(off + r) * p.tok_stride : 0;
+      const uint32_t dst = r * C::kRowBytes + ((c ^ (r & 7)) << 4);
+      cp_async_16(sK + dst, kbase + gofs, valid ? 16 : 0);
+      cp_async_16(sV + dst, vbase + gofs, valid ? 16 : 0);
+    }
+  };
+
+  // The first STAGES-1 tiles are on their way before anything that depends on q is touched.
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (s < n) issue(s);
+    cp_async_commit();
+  }
+
   // ---- Q^T B-fragments: head n = lane/4, dims 16ks + 2(lane%4) + {0,1} (+8) --------------------
   uint32_t qb[KS][2];
   {
@@ -167,47 +204,71 @@ paged_decode_kernel(const DecodeParams p) {
     }
   }
 
-  const uint32_t warp_smem = smem_u32(smem) + warp * C::kWarpBytes;
-  const int32_t* table = p.tables + static_cast<int64_t>(b) * p.max_blocks;
-  const bf16* kbase = p.kc + kvh * p.head_stride;
-  const bf16* vbase = p.vc + kvh * p.head_stride;
-
-  auto issue = [&](int i) {
-    const int s = i % STAGES;
-    const int tok_base = ((t0 + i) * NWARPS + warp) * 16;
-    int blk = -1, off = 0;
-    if (tok_base < ctx) {
-      const int bi = tok_base / p.block_size;
-      off = tok_base - bi * p.block_size;
-      if (bi < p.max_blocks) blk = __ldg(table + bi);
-    }
-    const uint32_t sK = warp_smem + s * C::kStageBytes;
-    const uint32_t sV = sK + C::kSubTileBytes;
-    const int c = lane % C::kChunks;
-    const int r0 = lane / C::kChunks;
-    const int64_t gofs0 = static_cast<int64_t>(blk < 0 ? 0 : blk) * p.blk_stride + c * 8;
+  // ---- FUSE: this step's own token is built while the first tiles fly: stored into the cache, and kept as row 0 of a
+  // private 16-token sub-tile (after the pipeline / merge buffers) that warp 0 of the last split scores after the loop ----
+  const int last_split = tiles_total == 0 ? 0 : (tiles_total - 1) / tps;  // the last split that owns any cached tile
+  const bool own_new = FUSE && split == last_split && warp == 0 && ctx_all > 0;
+  const uint32_t new_off = C::kSmemBytes;  // K sub-tile, then V sub-tile
+  if constexpr (FUSE) {
+    if (own_new) {
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-    for (int j = 0; j < C::kRowsPerLane; ++j) {
-      const int r = r0 + j * C::kRowStep;
-      const bool valid = (blk >= 0) && (tok_base + r < ctx);
-      const int64_t gofs = valid ? gofs0 + static_cast<int64_t>(off + r) * p.tok_stride : 0;
-      const uint32_t dst = r * C::kRowBytes + ((c ^ (r & 7)) << 4);
-      cp_async_16(sK + dst, kbase + gofs, valid ? 16 : 0);
-      cp_async_16(sV + dst, vbase + gofs, valid ? 16 : 0);
+      for (int j = 0; j < 2 * C::kSubTileBytes / (32 * 16); ++j)   // zero K and V sub-tiles (rows 1..15 must be finite)
+        *reinterpret_cast<uint4*>(smem + new_off + (j * 32 + lane) * 16) = z;
+      __syncwarp();
+      // lane l owns elements (2l, 2l+1) of each half of the row: exactly the RoPE pairs (j, j + D/2)
+      const bf16* krow = p.q + b * p.q_stride + static_cast<int64_t>(p.H + kvh) * D;
+      const bf16* vrow = p.q + b * p.q_stride + static_cast<int64_t>(p.H + p.Hkv + kvh) * D;
+      const uint32_t ka = *reinterpret_cast<const uint32_t*>(krow + 2 * lane);
+      const uint32_t kb2 = *reinterpret_cast<const uint32_t*>(krow + D / 2 + 2 * lane);
+      const uint32_t va = *reinterpret_cast<const uint32_t*>(vrow + 2 * lane);
+      const uint32_t vb = *reinterpret_cast<const uint32_t*>(vrow + D / 2 + 2 * lane);
+      float x1[2] = {bf16_lo(ka), bf16_hi(ka)}, x2[2] = {bf16_lo(kb2), bf16_hi(kb2)};
+      if (p.knw != nullptr) {
+        float ss = x1[0] * x1[0] + x2[0] * x2[0] + x1[1] * x1[1] + x2[1] * x2[1];
+        ss = warp_sum(ss);
+        const float inv = 1.0f / sqrtf(ss / static_cast<float>(D) + p.eps);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          x1[e] = __bfloat162float(__float2bfloat16_rn(x1[e] * inv * __bfloat162float(p.knw[2 * lane + e])));
+          x2[e] = __bfloat162float(__float2bfloat16_rn(x2[e] * inv * __bfloat162float(p.knw[D / 2 + 2 * lane + e])));
+        }
+      }
+      int64_t pos = __ldg(p.pos + b);
+      pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
+      const float* cs = p.cos_sin + pos * D;
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const float c = __ldg(cs + 2 * lane + e), sn = __ldg(cs + D / 2 + 2 * lane + e);
+        const float o1 = x1[e] * c - x2[e] * sn, o2 = x2[e] * c + x1[e] * sn;
+        x1[e] = o1; x2[e] = o2;
+      }
+      const uint32_t k1 = pack_bf16x2(x1[0], x1[1]), k2 = pack_bf16x2(x2[0], x2[1]);
+      // row 0 of the sub-tile (no swizzle for row 0: chunk c ^ 0)
+      uint32_t* k0s = reinterpret_cast<uint32_t*>(smem + new_off);
+      uint32_t* v0s = reinterpret_cast<uint32_t*>(smem + new_off + C::kSubTileBytes);
+      k0s[lane] = k1; k0s[D / 4 + lane] = k2;
+      v0s[lane] = va; v0s[D / 4 + lane] = vb;
+      if (grp == 0) {
+        const int slot = __ldg(p.slots + b);
+        if (slot >= 0) {
+          const int blk = slot / p.block_size, off = slot - blk * p.block_size;
+          const int64_t o = blk * p.blk_stride + off * p.tok_stride + kvh * p.head_stride;
+          *reinterpret_cast<uint32_t*>(p.kc_w + o + 2 * lane) = k1;
+          *reinterpret_cast<uint32_t*>(p.kc_w + o + D / 2 + 2 * lane) = k2;
+          *reinterpret_cast<uint32_t*>(p.vc_w + o + 2 * lane) = va;
+          *reinterpret_cast<uint32_t*>(p.vc_w + o + D / 2 + 2 * lane) = vb;
+        }
+      }
+      __syncwarp();
     }
-  };
+  }
 
   float m_run[2] = {-INFINITY, -INFINITY};
   float l_run[2] = {0.f, 0.f};
   float acc[KS][4];
 #pragma unroll
   for (int mt = 0; mt < KS; ++mt) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0.f;
-
-#pragma unroll
-  for (int s = 0; s < STAGES - 1; ++s) {
-    if (s < n) issue(s);
-    cp_async_commit();
-  }
 
   // One 16-token sub-tile of this warp: S^T = K.Q^T, online softmax, O^T += V^T.P^T.  Tokens >= lim are masked.
   auto process = [&](uint32_t sK, uint32_t sV, int tok_base, int lim) {
@@ -283,64 +344,7 @@ paged_decode_kernel(const DecodeParams p) {
   }
 
   if constexpr (FUSE) {
-    // ---- this step's own token: built here, stored into the cache, attended to from shared memory ----------------
-    const int last_split = tiles_total == 0 ? 0 : (tiles_total - 1) / tps;  // the last split that owns any cached tile
-    if (split == last_split && warp == 0 && ctx_all > 0) {
-      cp_async_wait<0>();
-      __syncwarp();
-      const uint32_t sK = warp_smem, sV = warp_smem + C::kSubTileBytes;
-      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-      for (int j = 0; j < 2 * C::kSubTileBytes / (32 * 16); ++j)   // zero K and V sub-tiles (rows 1..15 must be finite)
-        *reinterpret_cast<uint4*>(smem + warp * C::kWarpBytes + (j * 32 + lane) * 16) = z;
-      __syncwarp();
-      // lane l owns elements (2l, 2l+1) of each half of the row: exactly the RoPE pairs (j, j + D/2)
-      const bf16* krow = p.q + b * p.q_stride + static_cast<int64_t>(p.H + kvh) * D;
-      const bf16* vrow = p.q + b * p.q_stride + static_cast<int64_t>(p.H + p.Hkv + kvh) * D;
-      const uint32_t ka = *reinterpret_cast<const uint32_t*>(krow + 2 * lane);
-      const uint32_t kb2 = *reinterpret_cast<const uint32_t*>(krow + D / 2 + 2 * lane);
-      const uint32_t va = *reinterpret_cast<const uint32_t*>(vrow + 2 * lane);
-      const uint32_t vb = *reinterpret_cast<const uint32_t*>(vrow + D / 2 + 2 * lane);
-      float x1[2] = {bf16_lo(ka), bf16_hi(ka)}, x2[2] = {bf16_lo(kb2), bf16_hi(kb2)};
-      if (p.knw != nullptr) {
-        float ss = x1[0] * x1[0] + x2[0] * x2[0] + x1[1] * x1[1] + x2[1] * x2[1];
-        ss = warp_sum(ss);
-        const float inv = 1.0f / sqrtf(ss / static_cast<float>(D) + p.eps);
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          x1[e] = __bfloat162float(__float2bfloat16_rn(x1[e] * inv * __bfloat162float(p.knw[2 * lane + e])));
-          x2[e] = __bfloat162float(__float2bfloat16_rn(x2[e] * inv * __bfloat162float(p.knw[D / 2 + 2 * lane + e])));
-        }
-      }
-      int64_t pos = __ldg(p.pos + b);
-      pos = pos < 0 ? 0 : (pos >= p.max_position ? p.max_position - 1 : pos);
-      const float* cs = p.cos_sin + pos * D;
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const float c = __ldg(cs + 2 * lane + e), sn = __ldg(cs + D / 2 + 2 * lane + e);
-        const float o1 = x1[e] * c - x2[e] * sn, o2 = x2[e] * c + x1[e] * sn;
-        x1[e] = o1; x2[e] = o2;
-      }
-      const uint32_t k1 = pack_bf16x2(x1[0], x1[1]), k2 = pack_bf16x2(x2[0], x2[1]);
-      // row 0 of the sub-tile (no swizzle for row 0: chunk c ^ 0)
-      uint32_t* k0s = reinterpret_cast<uint32_t*>(smem + warp * C::kWarpBytes);
-      uint32_t* v0s = reinterpret_cast<uint32_t*>(smem + warp * C::kWarpBytes + C::kSubTileBytes);
-      k0s[lane] = k1; k0s[D / 4 + lane] = k2;
-      v0s[lane] = va; v0s[D / 4 + lane] = vb;
-      if (grp == 0) {
-        const int slot = __ldg(p.slots + b);
-        if (slot >= 0) {
-          const int blk = slot / p.block_size, off = slot - blk * p.block_size;
-          const int64_t o = blk * p.blk_stride + off * p.tok_stride + kvh * p.head_stride;
-          *reinterpret_cast<uint32_t*>(p.kc_w + o + 2 * lane) = k1;
-          *reinterpret_cast<uint32_t*>(p.kc_w + o + D / 2 + 2 * lane) = k2;
-          *reinterpret_cast<uint32_t*>(p.vc_w + o + 2 * lane) = va;
-          *reinterpret_cast<uint32_t*>(p.vc_w + o + D / 2 + 2 * lane) = vb;
-        }
-      }
-      __syncwarp();
-      process(sK, sV, ctx, ctx_all);
-    }
+    if (own_new) process(smem_u32(smem) + new_off, smem_u32(smem) + new_off + C::kSubTileBytes, ctx, ctx_all);
   }
 
   // ---- merge the NWARPS partial states through shared memory ------------------------------------
@@ -438,9 +442,10 @@ template <int D, int STAGES, int NWARPS, bool FUSE = false>
 static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
   using C = DecodeCfg<D, STAGES, NWARPS>;
   auto kern = paged_decode_kernel<D, STAGES, NWARPS, FUSE>;
-  NVLLM_SMEM_ATTR_ONCE(kern, C::kSmemBytes);
+  constexpr int kBytes = C::kSmemBytes + (FUSE ? 2 * C::kSubTileBytes : 0);  // + the step's own K/V sub-tile
+  NVLLM_SMEM_ATTR_ONCE(kern, kBytes);
   dim3 grid(p.num_splits, p.Hkv * p.ngrp, p.batch);
-  NVLLM_CUDA(launch_pdl(kern, grid, dim3(NWARPS * 32), C::kSmemBytes, stream, p));
+  NVLLM_CUDA(launch_pdl(kern, grid, dim3(NWARPS * 32), kBytes, stream, p));
   if (p.num_splits > 1)
     NVLLM_CUDA(launch_pdl(paged_decode_reduce_kernel<D>, dim3(p.H, p.batch), dim3(D), 0, stream, p));
   return 0;
