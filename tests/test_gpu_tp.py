@@ -284,7 +284,7 @@ def _ar_worker(rank, world, port, q):
                                res_eq=bool(torch.equal(h1.view(T, hid)[mine].float(), h0.view(T, hid)[mine].float())),
                                res_ref=float((h1.view(T, hid)[mine].float() - hnew[mine]).abs().max()) if mine.stop > mine.start else 0.0))
         # every rank must hold the same normed tensor bit for bit (receivers get the owner's bytes)
-        last = outs["1"][0].view(torch.int16)
+        last = outs["1"][0].view(torch.uint8)
         alls = [torch.empty_like(last) for _ in range(world)]
         dist.all_gather(alls, last)
         same = all(torch.equal(a, alls[0]) for a in alls)
