@@ -300,22 +300,6 @@ __device__ __forceinline__ uint4 ll_scrub(uint4 v) {
 __device__ __forceinline__ bool ll_arrived(const uint4& v) {
   return v.x != kLLEmpty && v.y != kLLEmpty && v.z != kLLEmpty && v.w != kLLEmpty;
 }
-// Re-polls one vector until it has arrived (slow path of the batched first attempt); same give-up rule as wait_flag.
-__device__ __noinline__ uint4 ll_spin(const void* p, long long timeout_cycles, uint32_t* dead, int* err) {
-  const long long t0 = clock64();
-  uint4 v = ld_sys_16(p);
-  while (!ll_arrived(v)) {
-    if (clock64() - t0 > timeout_cycles || *reinterpret_cast<volatile uint32_t*>(dead) != 0) {
-      *reinterpret_cast<volatile uint32_t*>(dead) = 1u;
-      *reinterpret_cast<volatile int*>(err) = 1;
-      __threadfence_system();
-      break;
-    }
-    v = ld_sys_16(p);
-  }
-  return v;
-}
-
 struct LLArParams {
   uint8_t* peer[8];          // symmetric regions of all ranks as mapped here
   uint8_t* self;
@@ -406,14 +390,32 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
         }
       }
       if (!dead) {
+        // Re-poll in ROUNDS: every vector that has not arrived is re-loaded in the same round (all in flight together), so
+        // a round costs one L2 round trip however many of the KCH x (WORLD-1) vectors are still missing.  (Spinning on
+        // them one after the other cost up to 14 round trips per thread at 8 ranks: 14.4 us per call instead of 8.4.)
+        long long t0 = 0;
+        while (true) {
+          bool miss = false;
 #pragma unroll
-        for (int k = 0; k < KCH; ++k) {
-          const int i = threadIdx.x + (k0 + k) * blockDim.x;
-          if (i < nvec) {
+          for (int k = 0; k < KCH; ++k)
 #pragma unroll
             for (int q = 0; q < WORLD; ++q)
-              if (q != p.rank && !ll_arrived(a[k][q]))
-                a[k][q] = ll_spin(st_row + static_cast<size_t>(q) * R * row_bytes + i * 16, p.timeout_cycles, dead_p, p.err);
+              miss |= (q != p.rank) && (threadIdx.x + (k0 + k) * blockDim.x < nvec) && !ll_arrived(a[k][q]);
+          if (!miss) break;
+          if (t0 == 0) t0 = clock64();
+          if (clock64() - t0 > p.timeout_cycles || *reinterpret_cast<volatile uint32_t*>(dead_p) != 0) {
+            *reinterpret_cast<volatile uint32_t*>(dead_p) = 1u;
+            *reinterpret_cast<volatile int*>(p.err) = 1;
+            __threadfence_system();
+            break;
+          }
+#pragma unroll
+          for (int k = 0; k < KCH; ++k) {
+            const int i = threadIdx.x + (k0 + k) * blockDim.x;
+#pragma unroll
+            for (int q = 0; q < WORLD; ++q)
+              if (q != p.rank && i < nvec && !ll_arrived(a[k][q]))
+                a[k][q] = ld_sys_16(st_row + static_cast<size_t>(q) * R * row_bytes + i * 16);
           }
         }
       }
@@ -481,13 +483,31 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
       const int i = threadIdx.x + k * blockDim.x;
       if (i < nvec) v[k] = ld_sys_16(src + i * 16);
     }
+    if (!dead) {
+      long long t0 = 0;
+      while (true) {  // rounds, as above
+        bool miss = false;
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) miss |= (threadIdx.x + k * blockDim.x < nvec) && !ll_arrived(v[k]);
+        if (!miss) break;
+        if (t0 == 0) t0 = clock64();
+        if (clock64() - t0 > p.timeout_cycles || *reinterpret_cast<volatile uint32_t*>(dead_p) != 0) {
+          *reinterpret_cast<volatile uint32_t*>(dead_p) = 1u;
+          *reinterpret_cast<volatile int*>(p.err) = 1;
+          __threadfence_system();
+          break;
+        }
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+          const int i = threadIdx.x + k * blockDim.x;
+          if (i < nvec && !ll_arrived(v[k])) v[k] = ld_sys_16(src + i * 16);
+        }
+      }
+    }
 #pragma unroll
     for (int k = 0; k < VPT; ++k) {
       const int i = threadIdx.x + k * blockDim.x;
-      if (i < nvec) {
-        if (!dead && !ll_arrived(v[k])) v[k] = ll_spin(src + i * 16, p.timeout_cycles, dead_p, p.err);
-        *reinterpret_cast<uint4*>(p.out + row * row_bytes + i * 16) = v[k];
-      }
+      if (i < nvec) *reinterpret_cast<uint4*>(p.out + row * row_bytes + i * 16) = v[k];
     }
   }
   // ---- the last CTA rotates the pair -------------------------------------------------------------------------------
