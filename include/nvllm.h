@@ -267,10 +267,26 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base);
  * `out` is complete on EVERY rank afterwards; `residual` is updated only for the rows this rank owns
  * (rows [rank*R, (rank+1)*R), R = ceil(num_tokens / world)) — it is a row-sharded stream whose only readers are
  * subsequent calls of this function with the same num_tokens.
- * out, x, residual: [num_tokens, hidden] bf16 buffers at identical offsets inside every rank's symmetric region.
+ * out, x, residual: [num_tokens, hidden] bf16 buffers at identical offsets inside every rank's symmetric region
+ * (required by the flag protocol; the push protocol only needs 16-byte alignment).
  * Bit-identical results on all ranks (each row is reduced once, by its owner, in fixed rank order). */
 int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
                                 int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream);
+/* Two protocols sit behind the call above.  Messages up to NVLLM_AR_LL_MAX_BYTES (8 MiB, decode batches) take the
+ * low-latency PUSH protocol: no flags, no fences — every 32-bit word of a not-yet-written buffer holds 0x80008000 (two bf16
+ * -0.0; senders map that one pattern to +0.0), partial rows are stored straight into the owner's stage buffer, the owner
+ * polls the data itself, reduces, and stores the normed rows into every peer's gather buffer, which the peer polls and
+ * copies to `out`; three buffer pairs rotate per call (NVLLM_AR_LL=0 disables it).  Larger messages (prefill) take the
+ * flag protocol with peer loads.  nvllm_comm_ll_applies: 1 when a [num_tokens, hidden] call takes the push protocol. */
+int nvllm_comm_ll_applies(const nvllm_comm* comm, int32_t num_tokens, int32_t hidden);
+/* RowParallelLinear::forward (linear.rs:228-239) whose all-reduce is the call below: y = x . w^T (bf16, m <= 512,
+ * n == ldy == hidden, nvllm_comm_ll_applies(comm, m, n)); the GEMM's epilogue stores the rows another rank reduces straight
+ * into that rank's stage buffer (they never touch y), so the transfer runs tile by tile under the GEMM's tail. */
+int nvllm_gemm_bf16_push(nvllm_comm* comm, void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
+                         int64_t ldx, int64_t ldw, int64_t ldy, void* stream);
+/* nvllm_allreduce_add_rmsnorm for an x produced by nvllm_gemm_bf16_push (same num_tokens / hidden): skips the push. */
+int nvllm_allreduce_add_rmsnorm_pushed(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
+                                       int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream);
 
 /* 0, or NVLLM_ERR_COMM once a fused kernel of this communicator gave up waiting for a peer (a rank died, or stalled for
  * longer than NVLLM_COMM_TIMEOUT_MS, default 10 min).  The kernel neither hangs nor traps: it raises this host-visible

@@ -71,6 +71,9 @@ PROTOTYPES = {
     "nvllm_comm_symm_alloc": (i32, [vp, sz, C.POINTER(vp)]),
     "nvllm_allreduce_add_rmsnorm": (i32, [vp, vp, vp, vp, vp, i32, i32, f32, i32, vp]),
     "nvllm_comm_error": (i32, [vp]),
+    "nvllm_comm_ll_applies": (i32, [vp, i32, i32]),
+    "nvllm_gemm_bf16_push": (i32, [vp, vp, vp, vp, i32, i32, i32, i64, i64, i64, vp]),
+    "nvllm_allreduce_add_rmsnorm_pushed": (i32, [vp, vp, vp, vp, vp, i32, i32, f32, i32, vp]),
     "nvllm_init_weight": (i32, [vp, i64, u64, u64, f32, i32, vp]),
 }
 

@@ -84,6 +84,8 @@ struct nvllm_comm {
 };
 
 namespace nvllm {
+int gemm_bf16_impl(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k, int64_t ldx, int64_t ldw,
+                   int64_t ldy, int32_t out_dtype, void* stream, const RowPush& ps);  // gemm_tcgen05.cu
 constexpr size_t kSymCtrlBytes = 4096;
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
@@ -285,18 +287,22 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
 // before this rank enters call i+1.  x / residual / out are ordinary local buffers for this kernel.
 // Every CTA waits for remote CTAs that may not have started: the grid must be co-resident (launch_fused_ar_ll sizes it
 // from the occupancy calculator), and phase A comes first in every CTA, unconditionally.
-constexpr uint32_t kLLEmpty = 0x80008000u;
 
-__device__ __forceinline__ void st_sys_16(void* p, const uint4& v) {
-  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+#ifdef NVLLM_TIMELINE
+// Debug build only (make timeline, tools/ar_timeline.py): thread 0 of every CTA stamps %globaltimer at the phase boundaries.
+__device__ unsigned long long* g_ar_tl_buf = nullptr;   // [cap][12]: {blockIdx, t0..t8, rows reduced, smid}
+__device__ unsigned int g_ar_tl_cursor = 0;
+__device__ unsigned int g_ar_tl_cap = 0;
+__device__ __forceinline__ unsigned long long ar_tl_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
 }
-__device__ __forceinline__ uint4 ll_scrub(uint4 v) {
-  v.x = v.x == kLLEmpty ? 0u : v.x;
-  v.y = v.y == kLLEmpty ? 0u : v.y;
-  v.z = v.z == kLLEmpty ? 0u : v.z;
-  v.w = v.w == kLLEmpty ? 0u : v.w;
-  return v;
-}
+#define ATL(i) do { if (threadIdx.x == 0) atl[i] = ar_tl_now(); } while (0)
+#else
+#define ATL(i) do { } while (0)
+#endif
+
 __device__ __forceinline__ bool ll_arrived(const uint4& v) {
   return v.x != kLLEmpty && v.y != kLLEmpty && v.z != kLLEmpty && v.w != kLLEmpty;
 }
@@ -309,6 +315,7 @@ struct LLArParams {
   const bf16* weight;
   size_t ll_off, ll_cap;     // low-latency area inside a region; bytes of one buffer
   int rank, num_tokens, hidden;
+  int pushed;                // phase A already happened in the epilogue of the producing GEMM (RowPush)
   float eps;
   long long timeout_cycles;
   int* err;
@@ -323,8 +330,14 @@ __device__ __forceinline__ uint8_t* peer_of(const LLArParams& p, unsigned q) {
 template <int WORLD, int VPT>
 __global__ void __launch_bounds__(512)
 allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
+#ifdef NVLLM_TIMELINE
+  unsigned long long atl[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  unsigned int atl_rows = 0;
+#endif
+  ATL(0);
   pdl_launch_dependents();
   pdl_wait();
+  ATL(1);
   uint32_t* ctrl = reinterpret_cast<uint32_t*>(p.self);
   const uint32_t b = ctrl[131];                          // pair of this call; advanced by the last CTA of the call
   const uint32_t bclr = b >= 1 ? b - 1 : 2;              // (b + 2) % 3
@@ -338,7 +351,7 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
   const int nvec = p.hidden >> 3;
 
   // ---- A: push my partial rows to their owners -------------------------------------------------------------------
-  for (int row = blockIdx.x; row < p.num_tokens; row += gridDim.x) {
+  for (int row = blockIdx.x; row < p.num_tokens && !p.pushed; row += gridDim.x) {
     const int owner = row / R;
     if (owner == p.rank) continue;
     const uint8_t* src = p.x + row * row_bytes;
@@ -355,6 +368,7 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
       if (i < nvec) st_sys_16(dst + i * 16, ll_scrub(v[k]));
     }
   }
+  ATL(2);  // partial rows pushed (stores issued)
   // ---- housekeeping while the pushes fly: clear the pair two calls ahead ------------------------------------------
   {
     uint4* c0 = reinterpret_cast<uint4*>(p.self + p.ll_off + static_cast<size_t>(bclr) * 2 * p.ll_cap);
@@ -363,6 +377,7 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
     const uint32_t n16 = clr_bytes >> 4;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) { c0[i] = e; c1[i] = e; }
   }
+  ATL(3);  // clear issued
   // ---- B: reduce + add + norm the rows I own, broadcast them -----------------------------------------------------
   const int row0 = p.rank * R;
   const int row1 = min(p.num_tokens, row0 + R);
@@ -445,6 +460,9 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
+#ifdef NVLLM_TIMELINE
+    if (atl_rows++ == 0) ATL(4);  // first owned row: every staged vector of the CTA has arrived
+#endif
     if (threadIdx.x < 32) {
       float t = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.f;
       t = warp_sum(t);
@@ -473,6 +491,7 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
     }
     __syncthreads();  // red / s_inv reuse
   }
+  ATL(5);  // owned rows reduced and broadcast
   // ---- C: gather the rows the other ranks own ----------------------------------------------------------------------
   for (int row = blockIdx.x; row < p.num_tokens; row += gridDim.x) {
     if (row / R == p.rank) continue;
@@ -510,8 +529,24 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
       if (i < nvec) *reinterpret_cast<uint4*>(p.out + row * row_bytes + i * 16) = v[k];
     }
   }
+  ATL(6);  // foreign rows gathered
   // ---- the last CTA rotates the pair -------------------------------------------------------------------------------
   __syncthreads();
+  ATL(7);
+#ifdef NVLLM_TIMELINE
+  if (threadIdx.x == 0 && g_ar_tl_buf != nullptr) {
+    const unsigned int slot = atomicAdd(&g_ar_tl_cursor, 1u);
+    if (slot < g_ar_tl_cap) {
+      unsigned long long* e = g_ar_tl_buf + static_cast<size_t>(slot) * 12;
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %%smid;\n" : "=r"(smid));
+      e[0] = blockIdx.x;
+      for (int i = 0; i < 9; ++i) e[1 + i] = atl[i];
+      e[10] = atl_rows;
+      e[11] = smid;
+    }
+  }
+#endif
   if (threadIdx.x == 0) {
     __threadfence();
     if (atomicAdd(ctrl + 135, 1u) == gridDim.x - 1) {
@@ -655,8 +690,50 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base) {
   return 0;
 }
 
+// 1 when a call of this size takes the low-latency push protocol (and may therefore be fed by nvllm_gemm_bf16_push).
+int nvllm_comm_ll_applies(const nvllm_comm* comm, int32_t num_tokens, int32_t hidden) {
+  using namespace nvllm;
+  if (!comm || !comm->sym_local || !knobs().ar_ll || num_tokens <= 0 || hidden <= 0) return 0;
+  if (comm->world != 2 && comm->world != 4 && comm->world != 8) return 0;
+  const int rows_per = (num_tokens + comm->world - 1) / comm->world;
+  return static_cast<size_t>(comm->world) * rows_per * hidden * 2 <= comm->ll_cap ? 1 : 0;
+}
+
+// y = x . w^T for a row-parallel projection under TP (o_proj / down_proj, linear.rs:228-239) whose output feeds
+// nvllm_allreduce_add_rmsnorm_pushed: rows this rank reduces itself land in y, every other row goes from the GEMM's
+// epilogue straight into the owner's low-latency stage buffer (m == the all-reduce's num_tokens, n == hidden == ldy).
+int nvllm_gemm_bf16_push(nvllm_comm* comm, void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
+                         int64_t ldx, int64_t ldw, int64_t ldy, void* stream) {
+  using namespace nvllm;
+  NVLLM_CHECK_ARG(comm && comm->sym_local, NVLLM_ERR_STATE, "gemm_bf16_push: no symmetric region");
+  NVLLM_CHECK_ARG(m > 0 && m <= 512 && ldy == n && nvllm_comm_ll_applies(comm, m, n), NVLLM_ERR_ARG,
+                  "gemm_bf16_push: m=%d n=%d ldy=%lld does not take the low-latency all-reduce", m, n, (long long)ldy);
+  RowPush ps;
+  for (int r = 0; r < 8; ++r) ps.peer[r] = r < comm->world ? comm->sym_peer[r] : nullptr;
+  ps.ctrl = reinterpret_cast<const uint32_t*>(comm->sym_local);
+  ps.ll_off = kSymCtrlBytes; ps.ll_cap = comm->ll_cap;
+  ps.rank = comm->rank; ps.R = (m + comm->world - 1) / comm->world; ps.hidden = n;
+  return gemm_bf16_impl(y, x, w, m, n, k, ldx, ldw, ldy, NVLLM_BF16, stream, ps);
+}
+
+static int allreduce_add_rmsnorm_any(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
+                                     int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream, bool pushed);
+
 int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
                                 int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream) {
+  return allreduce_add_rmsnorm_any(comm, out, x, residual, weight, num_tokens, hidden, eps, dtype, stream, false);
+}
+
+// The same, after nvllm_gemm_bf16_push produced x: the foreign rows are already on their way to their owners.
+int nvllm_allreduce_add_rmsnorm_pushed(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
+                                       int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream) {
+  NVLLM_CHECK_ARG(nvllm_comm_ll_applies(comm, num_tokens, hidden), NVLLM_ERR_ARG,
+                  "allreduce_add_rmsnorm_pushed: %d x %d does not take the low-latency protocol", num_tokens, hidden);
+  return allreduce_add_rmsnorm_any(comm, out, x, residual, weight, num_tokens, hidden, eps, dtype, stream, true);
+}
+
+static int allreduce_add_rmsnorm_any(nvllm_comm* comm, void* out, void* x, void* residual, const void* weight,
+                                     int32_t num_tokens, int32_t hidden, float eps, int32_t dtype, void* stream, bool pushed) {
   using namespace nvllm;
   NVLLM_CHECK_ARG(comm && comm->sym_local, NVLLM_ERR_STATE, "allreduce_add_rmsnorm: no symmetric region (nvllm_comm_symm_alloc)");
   NVLLM_CHECK_ARG(dtype == NVLLM_BF16, NVLLM_ERR_DTYPE, "allreduce_add_rmsnorm: dtype %d", dtype);
@@ -675,7 +752,7 @@ int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* resi
     q.x = static_cast<const uint8_t*>(x); q.res = static_cast<uint8_t*>(residual); q.out = static_cast<uint8_t*>(out);
     q.weight = static_cast<const bf16*>(weight);
     q.ll_off = kSymCtrlBytes; q.ll_cap = comm->ll_cap;
-    q.rank = comm->rank; q.num_tokens = num_tokens; q.hidden = hidden; q.eps = eps;
+    q.rank = comm->rank; q.num_tokens = num_tokens; q.hidden = hidden; q.eps = eps; q.pushed = pushed ? 1 : 0;
     q.timeout_cycles = knobs().comm_timeout_ms * 2000000ll;
     q.err = comm->d_err;
     switch (comm->world) {
@@ -707,6 +784,16 @@ int nvllm_allreduce_add_rmsnorm(nvllm_comm* comm, void* out, void* x, void* resi
   }
   NVLLM_CHECK_ARG(false, NVLLM_ERR_ARG, "allreduce_add_rmsnorm: world %d (2, 4 or 8)", comm->world);
 }
+
+#ifdef NVLLM_TIMELINE
+int nvllmdbg_ar_timeline(unsigned long long* d_buf, unsigned int cap) {
+  unsigned int zero = 0;
+  if (cudaMemcpyToSymbol(nvllm::g_ar_tl_buf, &d_buf, sizeof(d_buf)) != cudaSuccess) return 1;
+  if (cudaMemcpyToSymbol(nvllm::g_ar_tl_cap, &cap, sizeof(cap)) != cudaSuccess) return 1;
+  if (cudaMemcpyToSymbol(nvllm::g_ar_tl_cursor, &zero, sizeof(zero)) != cudaSuccess) return 1;
+  return 0;
+}
+#endif
 
 // 0, or NVLLM_ERR_COMM once a fused kernel of this communicator has given up waiting for a peer (sticky).
 int nvllm_comm_error(const nvllm_comm* comm) {

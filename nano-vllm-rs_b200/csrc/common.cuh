@@ -63,6 +63,7 @@ struct Knobs {
   int fuse_rope = 0;        // NVLLM_FUSE_ROPE: qkv GEMM epilogue with q/k-norm + RoPE + KV store
   int fuse_decode = 0;      // NVLLM_FUSE_DECODE: 1 = q/k-norm + RoPE + KV store inside the paged decode attention (first version measured 9 % slower)
   int fused_tp = 1;         // NVLLM_FUSED_TP: 0 = ncclAllReduce + separate add_rmsnorm
+  int gemm_push = 1;        // NVLLM_GEMM_PUSH: 0 = o_proj / down_proj write y locally and the all-reduce kernel pushes it
   int ar_ll = 1;            // NVLLM_AR_LL: 0 = always the flag-protocol fused all-reduce (no low-latency push variant)
   long long ar_ll_max_bytes = 8ll << 20;  // NVLLM_AR_LL_MAX_BYTES: largest message of the low-latency variant (6x this is reserved)
   int profile = 0;          // NVLLM_PROFILE: 1 = the runner times every launch of eager steps with CUDA events
@@ -127,6 +128,41 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+// ---- Low-latency tensor-parallel push (comm.cu) -------------------------------------------------------------------
+// kLLEmpty (two bf16 -0.0) marks "not written yet" in the low-latency buffers of the fused all-reduce: senders map that
+// one word to +0.0, receivers poll the data itself.  RowPush lets the PRODUCING GEMM's epilogue (o_proj / down_proj under
+// TP) store the rows of its partial sums that another rank reduces straight into that rank's stage buffer — phase A of
+// allreduce_add_rmsnorm_ll_kernel then happens tile by tile under the GEMM's tail instead of after it.
+constexpr uint32_t kLLEmpty = 0x80008000u;
+struct RowPush {
+  uint8_t* peer[8];      // symmetric regions of all ranks as mapped here
+  const uint32_t* ctrl;  // this rank's control block (pair index at [131]); nullptr = plain epilogue
+  size_t ll_off, ll_cap; // low-latency area inside a region, bytes of one buffer
+  int rank, R, hidden;   // rows per owner = ceil(tokens / world); row length in elements
+};
+__device__ __forceinline__ uint4 ll_scrub(uint4 v) {
+  v.x = v.x == kLLEmpty ? 0u : v.x;
+  v.y = v.y == kLLEmpty ? 0u : v.y;
+  v.z = v.z == kLLEmpty ? 0u : v.z;
+  v.w = v.w == kLLEmpty ? 0u : v.w;
+  return v;
+}
+__device__ __forceinline__ void st_sys_16(void* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// Row `row` of the partial-sum tensor: nullptr when this rank reduces it itself (store to y as usual), else where it goes
+// in the owner's stage buffer of the coming all-reduce call ([source rank][row within the owner's slice][hidden]).
+__device__ __forceinline__ bf16* push_row(const RowPush& ps, int row) {
+  const int owner = row / ps.R;
+  if (owner == ps.rank) return nullptr;
+  uint8_t* base = ps.peer[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) base = (owner == i) ? ps.peer[i] : base;  // no run-time index into the parameter block
+  const uint32_t b = ps.ctrl[131];
+  return reinterpret_cast<bf16*>(base + ps.ll_off + static_cast<size_t>(b) * 2 * ps.ll_cap +
+                                 (static_cast<size_t>(ps.rank) * ps.R + (row - owner * ps.R)) * ps.hidden * 2);
+}
 
 // ---- cp.async (LDGSTS) ---------------------------------------------------------------------------
 // 16-byte global->shared copy; src_bytes < 16 zero-fills the remainder (0 = pure zero fill).

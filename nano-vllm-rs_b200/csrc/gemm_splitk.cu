@@ -76,7 +76,7 @@ __device__ __forceinline__ void st_smem_f32(uint32_t addr, float v) {
 template <int BN, int SK, bool SILU>
 __global__ void __launch_bounds__(256, 1)
 gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                   bf16* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int STAGES) {
+                   bf16* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int STAGES, const RowPush ps) {
   using C = SkCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -234,6 +234,10 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
       static_assert(CW >= 8 && CW % 8 == 0, "slice must be whole 16-byte vectors");
       constexpr int CH = (CW % 16 == 0 && SK <= 4) ? 16 : 8;  // columns per iteration: CH * SK coalesced loads in flight
       bf16* dst = y + row * ldy + n_tile * BN + rank * CW;
+      bool remote = false;  // TP: the row is reduced by another rank -> straight into its low-latency stage buffer
+      if (ps.ctrl != nullptr && row < M) {
+        if (bf16* pr = push_row(ps, row)) { dst = pr + n_tile * BN + rank * CW; remote = true; }
+      }
 #pragma unroll 1
       for (int j = 0; j < CW; j += CH) {
         const int c0 = rank * CW + j;
@@ -252,9 +256,12 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
         }
         if (row < M) {
 #pragma unroll
-          for (int e = 0; e < CH; e += 8)
-            *reinterpret_cast<uint4*>(dst + j + e) = make_uint4(pack_bf16x2(a[e], a[e + 1]), pack_bf16x2(a[e + 2], a[e + 3]),
-                                                                pack_bf16x2(a[e + 4], a[e + 5]), pack_bf16x2(a[e + 6], a[e + 7]));
+          for (int e = 0; e < CH; e += 8) {
+            const uint4 o = make_uint4(pack_bf16x2(a[e], a[e + 1]), pack_bf16x2(a[e + 2], a[e + 3]),
+                                       pack_bf16x2(a[e + 4], a[e + 5]), pack_bf16x2(a[e + 6], a[e + 7]));
+            if (remote) st_sys_16(dst + j + e, ll_scrub(o));
+            else *reinterpret_cast<uint4*>(dst + j + e) = o;
+          }
         }
       }
     }
@@ -296,7 +303,7 @@ int splitk_stages(int kb_per) {
 
 template <int BN, int SK, bool SILU>
 int launch_splitk(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy, int tiles,
-                  int num_m_tiles, cudaStream_t st) {
+                  int num_m_tiles, cudaStream_t st, const RowPush& ps) {
   using C = SkCfg<BN>;
   auto kern = gemm_splitk_kernel<BN, SK, SILU>;
   NVLLM_SMEM_ATTR_ONCE(kern, C::smem_bytes(C::kMaxStages));
@@ -313,7 +320,7 @@ int launch_splitk(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, 
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<bf16*>(y), M, N, K, ldy, num_m_tiles, stages));
+  NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<bf16*>(y), M, N, K, ldy, num_m_tiles, stages, ps));
   return 0;
 }
 
@@ -375,7 +382,7 @@ namespace nvllm {
 #endif
 
 int gemm_splitk_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw, int64_t ldy,
-                         bool silu, int bn, int sk, cudaStream_t st) {
+                         bool silu, int bn, int sk, cudaStream_t st, const RowPush& ps) {
   CUtensorMap tx, tw;
   const int n_acc = silu ? 2 * n : n;
   if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 128)) return rc;
@@ -383,8 +390,8 @@ int gemm_splitk_dispatch(void* y, const void* x, const void* w, int m, int n, in
   const int mt = (m + 127) / 128, tiles = mt * (n_acc / bn);
 #define NVLLM_SK(BNV, SKV)                                                                                   \
   if (bn == BNV && sk == SKV)                                                                                \
-    return silu ? launch_splitk<BNV, SKV, true>(tx, tw, y, m, n, k, ldy, tiles, mt, st)                      \
-                : launch_splitk<BNV, SKV, false>(tx, tw, y, m, n, k, ldy, tiles, mt, st)
+    return silu ? launch_splitk<BNV, SKV, true>(tx, tw, y, m, n, k, ldy, tiles, mt, st, RowPush{})                      \
+                : launch_splitk<BNV, SKV, false>(tx, tw, y, m, n, k, ldy, tiles, mt, st, ps)
   NVLLM_SK(256, 8); NVLLM_SK(256, 4); NVLLM_SK(256, 2);
   NVLLM_SK(128, 8); NVLLM_SK(128, 4); NVLLM_SK(128, 2);
   NVLLM_SK(64, 4); NVLLM_SK(64, 2);

@@ -49,6 +49,20 @@ __device__ __forceinline__ void store_row32<bf16>(bf16* dst, const uint32_t (&r)
     }
   }
 }
+// The same 32 columns into a peer's low-latency stage buffer (RowPush): scrubbed, system-scope stores.
+__device__ __forceinline__ void push_row32(bf16* dst, const uint32_t (&r)[32], int col0, int n) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (col0 + j * 8 < n) {
+      uint4 v;
+      v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+      v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+      v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+      v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+      st_sys_16(dst + j * 8, ll_scrub(v));
+    }
+  }
+}
 template <>
 __device__ __forceinline__ void store_row32<float>(float* dst, const uint32_t (&r)[32], int col0, int n) {
 #pragma unroll
@@ -86,7 +100,7 @@ template <int BN, typename OutT, bool SILU, int CN, bool ROPE = false>
 __global__ void __launch_bounds__(256, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                     OutT* __restrict__ y, int M, int N, int K, int64_t ldy, int num_m_tiles, int num_tiles,
-                    const RopeEpi re = RopeEpi{}, int STAGES = GemmCfg<BN>::kStages) {
+                    const RopeEpi re = RopeEpi{}, int STAGES = GemmCfg<BN>::kStages, const RowPush ps = RowPush{}) {
   using C = GemmCfg<BN>;  // STAGES <= C::kStages: ring depth of this launch (fewer stages -> two CTAs per SM, see launch_gemm)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B tiles: 1024-byte aligned
@@ -298,13 +312,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           if (row < M && col0 < N) store_row32<OutT>(y + row * ldy + col0, g, col0, N);
         }
       } else {
+        bf16* remote = nullptr;  // TP: this row is reduced by another rank -> straight into its stage buffer
+        if constexpr (sizeof(OutT) == 2) {
+          if (ps.ctrl != nullptr && row < M) remote = push_row(ps, row);
+        }
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           uint32_t r[32];
           tmem_ld_32x32b_x32(taddr + c * 32, r);
           tmem_ld_wait();
           const int col0 = n_tile * BN + c * 32;
-          if (row < M && col0 < N) store_row32<OutT>(y + row * ldy + col0, r, col0, N);
+          if (row < M && col0 < N) {
+            if (remote != nullptr) push_row32(remote + col0, r, col0, N);
+            else store_row32<OutT>(y + row * ldy + col0, r, col0, N);
+          }
         }
       }
       tc_fence_before();
@@ -323,7 +344,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 
 template <int BN, typename OutT, bool SILU = false, int CN = 1, bool ROPE = false>
 static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, int M, int N, int K, int64_t ldy,
-                       cudaStream_t st, const RopeEpi& re = RopeEpi{}) {
+                       cudaStream_t st, const RopeEpi& re = RopeEpi{}, const RowPush& ps = RowPush{}) {
   using C = GemmCfg<BN>;
   auto kern = gemm_tcgen05_kernel<BN, OutT, SILU, CN, ROPE>;
   NVLLM_SMEM_ATTR_ONCE(kern, C::kSmemBytes);
@@ -343,7 +364,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
   const int smem = C::kSmemBytes - (C::kStages - stages) * C::kStageBytes;
   if constexpr (CN == 1) {
     NVLLM_CUDA(launch_pdl(kern, dim3(clusters), dim3(256), smem, st, tx, tw, static_cast<OutT*>(y), M, N, K, ldy,
-                          num_m_tiles, num_tiles, re, stages));
+                          num_m_tiles, num_tiles, re, stages, ps));
   } else {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(clusters * CN);
@@ -358,7 +379,7 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     NVLLM_CUDA(cudaLaunchKernelEx(&cfg, kern, tx, tw, static_cast<OutT*>(y), M, N, K, ldy, num_m_tiles, num_tiles, re,
-                                  static_cast<int>(C::kStages)));
+                                  static_cast<int>(C::kStages), ps));
   }
   return 0;
 }
@@ -388,7 +409,7 @@ int gemm_silu_2cta_dispatch(void* y, const void* x, const void* w, int m, int in
 // gemm_splitk.cu: cluster split-K for decode-sized projections (m <= 256)
 bool splitk_choose(int m, int n_acc, int k, bool silu, int bn_default, int* out_bn, int* out_sk);
 int gemm_splitk_dispatch(void* y, const void* x, const void* w, int m, int n, int k, int64_t ldx, int64_t ldw, int64_t ldy,
-                         bool silu, int bn, int sk, cudaStream_t st);
+                         bool silu, int bn, int sk, cudaStream_t st, const RowPush& ps = RowPush{});
 
 static bool use_2cta();
 // CTA pairs pay off once there are at least two 256-row tiles or the problem is large enough to fill the machine with
@@ -420,11 +441,12 @@ static bool use_2cta() {
 
 extern "C" size_t nvllm_gemm_workspace_bytes(int32_t, int32_t, int32_t) { return 0; }
 
-extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
-                               int64_t ldx, int64_t ldw, int64_t ldy, int32_t out_dtype, void* workspace,
-                               size_t workspace_bytes, void* stream) {
-  using namespace nvllm;
-  (void)workspace; (void)workspace_bytes;
+namespace nvllm {
+// y = x . w^T.  ps.ctrl != nullptr (bf16 output, n == ldy == ps.hidden, m <= 512): rows another TP rank reduces are
+// pushed into that rank's low-latency stage buffer by the epilogue instead of being written to y (see RowPush).
+int gemm_bf16_impl(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k, int64_t ldx, int64_t ldw,
+                   int64_t ldy, int32_t out_dtype, void* stream, const RowPush& ps) {
+  const bool push = ps.ctrl != nullptr;
   NVLLM_CHECK_ARG(m >= 0 && n > 0 && k > 0, NVLLM_ERR_ARG, "gemm: m=%d n=%d k=%d", m, n, k);
   NVLLM_CHECK_ARG(k % 64 == 0 && n % 8 == 0, NVLLM_ERR_ARG, "gemm: need k %% 64 == 0 and n %% 8 == 0 (k=%d n=%d)", k, n);
   NVLLM_CHECK_ARG(ldx >= k && ldw >= k && ldy >= n && ldx % 8 == 0 && ldw % 8 == 0 && ldy % 8 == 0, NVLLM_ERR_ALIGN,
@@ -436,14 +458,14 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   if (out_dtype == NVLLM_BF16) {  // decode-sized, long-K projections: split K over a cluster (gemm_splitk.cu)
     int sbn = 0, ssk = 0;
     if (splitk_choose(m, n, k, false, pick_bn(m, n), &sbn, &ssk))
-      return gemm_splitk_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, false, sbn, ssk, st);
+      return gemm_splitk_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, false, sbn, ssk, st, ps);
   }
-  if (want_2cta(m, n, k)) return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, st);
+  if (!push && want_2cta(m, n, k)) return gemm_2cta_dispatch(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, st);
   const int bn = pick_bn(m, n);
   CUtensorMap tx, tw;
   // x-multicast clusters of 4 along N: worth it when x (re-read once per n-tile) dominates the L2 -> SM traffic,
   // i.e. several n-tiles of a narrow width and a long K.
-  if (use_mcast() && bn <= 64 && n % (4 * bn) == 0 && k >= 2048 && out_dtype == NVLLM_BF16) {
+  if (!push && use_mcast() && bn <= 64 && n % (4 * bn) == 0 && k >= 2048 && out_dtype == NVLLM_BF16) {
     if (int rc = make_tmap_bf16_2d(&tx, x, m, k, ldx, 32)) return rc;
     if (int rc = make_tmap_bf16_2d(&tw, w, n, k, ldw, bn)) return rc;
     return bn == 64 ? launch_gemm<64, bf16, false, 4>(tx, tw, y, m, n, k, ldy, st)
@@ -453,7 +475,7 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
   if (int rc = make_tmap_bf16_2d(&tw, w, n, k, ldw, bn)) return rc;
 #define NVLLM_GEMM_CASE(BNV)                                                                     \
   case BNV:                                                                                      \
-    return out_dtype == NVLLM_BF16 ? launch_gemm<BNV, bf16>(tx, tw, y, m, n, k, ldy, st)         \
+    return out_dtype == NVLLM_BF16 ? launch_gemm<BNV, bf16>(tx, tw, y, m, n, k, ldy, st, RopeEpi{}, ps) \
                                    : launch_gemm<BNV, float>(tx, tw, y, m, n, k, ldy, st)
   switch (bn) {
     NVLLM_GEMM_CASE(256);
@@ -463,6 +485,14 @@ extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m,
       NVLLM_GEMM_CASE(32);
   }
 #undef NVLLM_GEMM_CASE
+}
+}  // namespace nvllm
+
+extern "C" int nvllm_gemm_bf16(void* y, const void* x, const void* w, int32_t m, int32_t n, int32_t k,
+                               int64_t ldx, int64_t ldw, int64_t ldy, int32_t out_dtype, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  (void)workspace; (void)workspace_bytes;
+  return nvllm::gemm_bf16_impl(y, x, w, m, n, k, ldx, ldw, ldy, out_dtype, stream, nvllm::RowPush{});
 }
 
 // MergedColumnParallelLinear::forward + SiluAndMul::forward in one call (linear.rs:437-439 + activation.rs:46-63).

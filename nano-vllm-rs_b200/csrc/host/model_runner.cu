@@ -473,10 +473,21 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
   };
   // h += all-reduce(proj); normed = rmsnorm(h) * w — the reference's RowParallelLinear all-reduce TODO (linear.rs:236)
   // followed by the residual add + norm: one fused kernel over NVLink peer memory, or NCCL + add_rmsnorm.
+  // Decode-sized batches under TP: o_proj / down_proj push the rows another rank reduces straight from their epilogue
+  // into that rank's stage buffer (nvllm_gemm_bf16_push), and the fused all-reduce skips its own push phase.
+  const bool push = tp > 1 && fused_tp && knobs().gemm_push && N <= 512 && nvllm_comm_ll_applies(comm, N, hidden);
+  auto row_gemm = [&](const void* x, const void* w, int k, const char* what) -> int {
+    if (!push) return gemm(proj, x, w, hidden, k, hidden, NVLLM_BF16, what);
+    ++launches;
+    const int rc = nvllm_gemm_bf16_push(comm, proj, x, w, N, hidden, k, k, k, hidden, st);
+    mark(what);
+    return rc;
+  };
   auto add_norm = [&](const bf16* w) -> int {
     if (tp > 1 && fused_tp) {
       ++launches;
-      const int rc = nvllm_allreduce_add_rmsnorm(comm, normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
+      const int rc = push ? nvllm_allreduce_add_rmsnorm_pushed(comm, normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st)
+                          : nvllm_allreduce_add_rmsnorm(comm, normed, proj, h, w, N, hidden, eps, NVLLM_BF16, st);
       mark("allreduce_add_rmsnorm (fused TP epilogue)");
       return rc;
     }
@@ -533,14 +544,14 @@ int nvllm_runner::forward(int N, int S, bool is_prefill, bool paged_prefill, con
                                          &layout, scale, NVLLM_BF16, st)); ++launches;
       mark(paged_prefill ? "prefill_attention (paged prefix)" : "prefill_attention");
     }
-    RUN(gemm(proj, attn, w.o, hidden, HD, hidden, NVLLM_BF16, "o_proj GEMM"));
+    RUN(row_gemm(attn, w.o, HD, "o_proj GEMM"));
     RUN(add_norm(w.post_ln));                                                                                          // qwen3.rs:382-385
     // gate_up GEMM with the SiLU*mul in its epilogue (MergedColumnParallelLinear + SiluAndMul, qwen3.rs:307-310)
     RUN(nvllm_gemm_silu_mul_bf16(act, normed, w.gate_up, N, inter, hidden, hidden, hidden, inter, gate_up,
                                  static_cast<size_t>(max_tokens) * 2 * inter * 2, st));
     launches += (inter % 128 == 0) ? 1 : 2;
     mark("gate_up_proj GEMM + SiLU*mul");
-    RUN(gemm(proj, act, w.down, hidden, inter, hidden, NVLLM_BF16, "down_proj GEMM"));
+    RUN(row_gemm(act, w.down, inter, "down_proj GEMM"));
   }
   RUN(add_norm(final_norm));                                                                                           // qwen3.rs:389,501
   const bf16* head_in = normed;
