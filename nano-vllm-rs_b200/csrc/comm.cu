@@ -390,6 +390,12 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
     const uint8_t* st_row = p.self + stage_off + static_cast<size_t>(row - row0) * row_bytes;  // + q * R * row_bytes
     uint32_t sw[VPT][4];
     float ss = 0.f;
+    uint4 wreg[VPT];  // norm weights: requested before the polls, not after the row statistic (one L2 latency off the path)
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int i = threadIdx.x + k * blockDim.x;
+      if (i < nvec) wreg[k] = __ldg(wv + i);
+    }
 #pragma unroll
     for (int k0 = 0; k0 < VPT; k0 += KCH) {
       uint4 a[KCH][WORLD], r[KCH];
@@ -474,8 +480,7 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
     for (int k = 0; k < VPT; ++k) {
       const int i = threadIdx.x + k * blockDim.x;
       if (i < nvec) {
-        const uint4 w = __ldg(wv + i);
-        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+        const uint32_t ww[4] = {wreg[k].x, wreg[k].y, wreg[k].z, wreg[k].w};
         uint4 o;
         uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
 #pragma unroll

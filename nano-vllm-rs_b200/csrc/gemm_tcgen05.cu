@@ -386,16 +386,28 @@ static int launch_gemm(const CUtensorMap& tx, const CUtensorMap& tw, void* y, in
 
 static int pick_bn(int M, int N) {
   const int forced = knobs().gemm_bn;  // benchmarking knob (nvllm_reload_env() lets one process sweep it)
-  if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
+  if (forced == 32 || forced == 64 || forced == 128 || forced == 192 || forced == 256) return forced;
   const int sms = sm_count();
   const long mt = (M + 127) / 128;
-  const int cands[4] = {32, 64, 128, 256};
+  const int cands[5] = {32, 64, 128, 192, 256};
   // Small problems (decode): the narrowest tile that still fits in ONE wave — maximum number of CTAs streaming the
-  // weights concurrently, no second (serialised, latency-bound) pass over the persistent loop.
-  for (int i = 0; i < 4; ++i) {
+  // weights concurrently, no second (serialised, latency-bound) pass over the persistent loop.  (192 exists for the
+  // 512-row TP batches: 4 x N/256 tiles often fill only 2/3 of the SMs, or spill a third of a wave into a second one.)
+  for (int i = 0; i < 5; ++i) {
     const long tiles = mt * ((N + cands[i] - 1) / cands[i]);
     if (tiles <= sms) return cands[i];
   }
+  // A few waves (M = 512 decode batches on the wide projections): the makespan is waves x tile width.
+  long best_cost = 0;
+  int best = 256;
+  for (int i = 4; i >= 2; --i) {
+    const long tiles = mt * ((N + cands[i] - 1) / cands[i]);
+    const long waves = (tiles + sms - 1) / sms;
+    if (waves > 4) continue;
+    const long cost = waves * cands[i];
+    if (best_cost == 0 || cost < best_cost) { best_cost = cost; best = cands[i]; }  // ties keep the wider tile
+  }
+  if (best_cost != 0) return best;
   // Large problems (prefill, LM head): widest tile = highest MMA efficiency and operand reuse.
   return 256;
 }
@@ -479,6 +491,7 @@ int gemm_bf16_impl(void* y, const void* x, const void* w, int32_t m, int32_t n, 
                                    : launch_gemm<BNV, float>(tx, tw, y, m, n, k, ldy, st)
   switch (bn) {
     NVLLM_GEMM_CASE(256);
+    NVLLM_GEMM_CASE(192);
     NVLLM_GEMM_CASE(128);
     NVLLM_GEMM_CASE(64);
     default:
@@ -522,6 +535,7 @@ extern "C" int nvllm_gemm_silu_mul_bf16(void* out, const void* x, const void* w_
     if (int rc = make_tmap_bf16_2d(&tw, w_gate_up, 2 * static_cast<int64_t>(inter), k, ldw, bn / 2)) return rc;
     switch (bn) {
       case 256: return launch_gemm<256, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
+      case 192: return launch_gemm<192, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
       case 128: return launch_gemm<128, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
       default: return launch_gemm<64, bf16, true>(tx, tw, out, m, inter, k, ldout, st);
     }

@@ -21,3 +21,34 @@ def cuda():
     lib = _ffi.lib()  # raises if the extension is missing: GPU tests must never pass on a fallback
     assert lib.nvllm_device_ok() == 1, "libnvllm.so loaded but no sm_100 device visible"
     return torch.device("cuda:0")
+
+
+@pytest.fixture(autouse=True)
+def _nvllm_knobs_follow_the_environment(monkeypatch):
+    """libnvllm.so parses its NVLLM_* knobs once (nvllm::knobs()); tests that force a kernel variant with
+    monkeypatch.setenv / delenv must have the library re-read them — and again once the environment is restored."""
+    touched = []
+
+    def reload():
+        from nano_vllm_rs_b200 import _ffi
+        _ffi.lib().nvllm_reload_env()
+
+    set_orig, del_orig = monkeypatch.setenv, monkeypatch.delenv
+
+    def setenv(name, value, *a, **k):
+        set_orig(name, value, *a, **k)
+        if name.startswith("NVLLM_"):
+            touched.append(name)
+            reload()
+
+    def delenv(name, *a, **k):
+        del_orig(name, *a, **k)
+        if name.startswith("NVLLM_"):
+            touched.append(name)
+            reload()
+
+    monkeypatch.setenv, monkeypatch.delenv = setenv, delenv
+    yield
+    if touched:
+        monkeypatch.undo()
+        reload()

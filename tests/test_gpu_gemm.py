@@ -32,7 +32,7 @@ def test_gemm_vs_oracle(cuda, m, n, k, out_dtype):
     assert_close(to_np_f32(y), ref, ATOL if out_dtype == torch.bfloat16 else 2e-3, RTOL if out_dtype == torch.bfloat16 else 1e-4, f"gemm {m}x{n}x{k}")
 
 
-@pytest.mark.parametrize("bn", ["32", "64", "128", "256"])
+@pytest.mark.parametrize("bn", ["32", "64", "128", "192", "256"])
 def test_gemm_every_tile_width(cuda, bn, monkeypatch):
     """Force each BLOCK_N instantiation (the heuristic would otherwise hide some) in a fresh process."""
     import subprocess, sys, os
@@ -100,6 +100,28 @@ def test_gemm_silu_mul_fused_equals_unfused(cuda, m, inter, k, monkeypatch):
     if m * inter * k < 2 ** 28:   # and against the CPU oracle where it is cheap
         want = O.silu_and_mul(O.linear(to_np_f32(x), to_np_f32(w)))
         assert_close(to_np_f32(fused), want, ATOL, 2 ** -6, "gemm_silu_mul vs oracle")
+
+
+@pytest.mark.parametrize("m,n,k,silu", [(512, 6144, 4096, False), (512, 6144, 4096, True), (256, 12288, 1024, True), (300, 1000, 512, False)])
+def test_gemm_192_wide_tiles(cuda, m, n, k, silu, monkeypatch):
+    """The 192-column tile (M = 512 TP decode batches on the wide projections: 4 x N/256 tiles fill 2/3 of the SMs or
+    spill into a second wave) forced on plain and SiLU shapes, incl. an N that 192 does not divide: bit-identical to the
+    256-wide tile (same k order, same f32 accumulation) and within tolerance of the CUDA-core check kernel."""
+    from nano_vllm_rs_b200 import ops
+    monkeypatch.setenv("NVLLM_GEMM_SPLITK", "0")
+    g = torch.Generator(device="cuda").manual_seed(m + n + k)
+    x = torch.randn((m, k), generator=g, device=cuda).to(torch.bfloat16)
+    w = (torch.randn(((2 if silu else 1) * n, k), generator=g, device=cuda) * 0.03).to(torch.bfloat16)
+    fn = (lambda: ops.gemm_silu_mul(x, w)) if silu else (lambda: ops.gemm_bf16(x, w))
+    monkeypatch.setenv("NVLLM_GEMM_BN", "256")
+    y256 = fn()
+    monkeypatch.setenv("NVLLM_GEMM_BN", "192")
+    y192 = fn()
+    torch.cuda.synchronize()
+    assert torch.equal(y192, y256)
+    if not silu:
+        r = ops.gemm_bf16(x, w, out_dtype=torch.float32, simt=True)
+        assert_close(to_np_f32(y192), to_np_f32(r), ATOL, RTOL, "192-wide tile vs check kernel")
 
 
 @pytest.mark.parametrize("kind", ["reference", "head_major"])
