@@ -16,12 +16,17 @@ SHAPES = {  # name: (M, N, K, kind)
     "32B/tp8 m64 gate_up+silu": (64, 3200, 5120, "silu"), "32B/tp8 m64 down": (64, 5120, 3200, "gemm"),
     "8B/tp2 qkv": (512, 3072, 4096, "gemm"), "8B/tp2 o": (512, 4096, 2048, "gemm"), "8B/tp2 gate_up+silu": (512, 6144, 4096, "silu"),
     "8B/tp2 down": (512, 4096, 6144, "gemm"),
+    "8B m512 qkv": (512, 6144, 4096, "gemm"), "8B m512 o": (512, 4096, 4096, "gemm"), "8B m512 gate_up+silu": (512, 12288, 4096, "silu"),
+    "8B m512 down": (512, 4096, 12288, "gemm"),
+    "8B/tp4 qkv": (512, 1536, 4096, "gemm"), "8B/tp4 o": (512, 4096, 1024, "gemm"), "8B/tp4 gate_up+silu": (512, 3072, 4096, "silu"),
+    "8B/tp4 down": (512, 4096, 3072, "gemm"),
     "8B/tp8 qkv": (512, 768, 4096, "gemm"), "8B/tp8 o": (512, 4096, 512, "gemm"), "8B/tp8 gate_up+silu": (512, 1536, 4096, "silu"),
     "8B/tp8 down": (512, 4096, 1536, "gemm"),
 }
 S, T, G = "NVLLM_GEMM_SPLITK", "NVLLM_GEMM_SK_STAGES", "NVLLM_GEMM_STAGES"
 KNOBS = [{}, {S: "0"}, {S: "64,4"}, {S: "64,2"}, {S: "128,4"}, {S: "128,2"}, {S: "256,4"}, {S: "256,2"},
-         {S: "0", "NVLLM_GEMM_MCAST": "1"}, {S: "0", "NVLLM_GEMM_2CTA": "2"}]
+         {S: "0", "NVLLM_GEMM_MCAST": "1"}, {S: "0", "NVLLM_GEMM_2CTA": "2"},
+         {S: "0", "NVLLM_GEMM_BN": "128"}, {S: "0", "NVLLM_GEMM_BN": "192"}, {S: "0", "NVLLM_GEMM_BN": "256"}, {S: "128,8"}, {S: "256,8"}]
 ALL = ("NVLLM_GEMM_BN", "NVLLM_GEMM_MCAST", "NVLLM_GEMM_2CTA", S, T, G)
 
 
@@ -54,12 +59,14 @@ def run(name, M, N, K, kind, layers, reps):
 
 def main():
     ap = argparse.ArgumentParser(); ap.add_argument("--layers", type=int, default=28); ap.add_argument("--reps", type=int, default=20)
-    ap.add_argument("--only", default="")
+    ap.add_argument("--only", default=""); ap.add_argument("--knobs", default="", help="comma list of indices into KNOBS")
     a = ap.parse_args()
     for name, (M, N, K, kind) in SHAPES.items():
         if a.only and not any(o in name for o in a.only.split(",")):
             continue
-        for kn in KNOBS:
+        for ki, kn in enumerate(KNOBS):
+            if a.knobs and str(ki) not in a.knobs.split(","):
+                continue
             for k in ALL:
                 os.environ.pop(k, None)
             os.environ.update(kn)
