@@ -475,21 +475,15 @@ extern "C" int nvllm_paged_decode_choose_splits(int32_t batch, int32_t num_heads
   long max_s = max_context_len / 256;          // keep >= 256 tokens per split
   if (max_s < 1) max_s = 1;
   if (max_s > 64) max_s = 64;
-  if (base >= 8 * slots) return 1;             // many waves already: quantisation loss < 1/8 wave
-  // Wave-aware choice: the grid runs in waves of `slots` CTAs; pick the split count whose last wave is fullest (e.g.
-  // 512 CTAs on 296 slots = 1.73 waves -> 4 splits = 6.9 waves), discounted by the cost of the partials
-  // (each split adds one fp32 [H, D] partial per sequence + the reduce kernel).
-  int best = 1;
-  double best_score = -1.0;
-  for (long sp = 1; sp <= max_s; ++sp) {
-    const long ctas = base * sp;
-    const long waves = (ctas + slots - 1) / slots;
-    double eff = static_cast<double>(ctas) / static_cast<double>(waves * slots);
-    if (sp > 1) eff *= (1.0 - 0.02 - 0.004 * static_cast<double>(sp));
-    if (eff > best_score + 1e-9) { best_score = eff; best = static_cast<int>(sp); }
-    if (ctas >= 8 * slots) break;
-  }
-  return best;
+  // Measured (profiles/r02_decode_split_sweep.jsonl, 512 seqs x 1536 tokens, Hkv = 1 / 2 / 4 / 8 per rank): once the grid
+  // holds a full wave, ONE split wins at every shard shape — 5.94 vs 5.16 TB/s at Hkv = 1 (512 CTAs = 1.73 waves), where
+  // round 1's wave-filling model picked 4.  A split costs its f32 partials, a second launch and shorter CTAs (6-24 % at
+  // 2-8 splits); dynamic CTA scheduling already hides most of a ragged last wave.  Split only to FILL the first wave
+  // (few sequences x long contexts: 64 x 32.5K at Hkv = 1 -> 4 splits = 256 CTAs, the measured best).
+  if (base >= slots) return 1;
+  long sp = slots / base;
+  if (sp > max_s) sp = max_s;
+  return sp < 1 ? 1 : static_cast<int>(sp);
 }
 
 namespace nvllm {
@@ -587,6 +581,8 @@ static int decode_dispatch(void* out, const void* q, void* k_cache, void* v_cach
       case 2: return launch_decode<128, 3, 8>(p, st);
       case 3: return launch_decode<128, 2, 4>(p, st);   // 64 KiB smem: 3 CTAs / SM
       case 4: return launch_decode<128, 4, 2>(p, st);   // 2 warps x 4 stages, 64 KiB: 3 CTAs / SM
+      case 5: return launch_decode<128, 3, 2>(p, st);   // 2 warps x 3 stages, 48 KiB: 4 CTAs / SM
+      case 6: return launch_decode<128, 6, 2>(p, st);   // 2 warps x 6 stages, 96 KiB: 2 CTAs / SM, deeper per-warp pipeline
       default: return launch_decode<128, 3, 4>(p, st);
     }
   }

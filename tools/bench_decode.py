@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--block-size", type=int, default=256)
     ap.add_argument("--layout", default="head_major", choices=["head_major", "reference"])
     ap.add_argument("--splits", type=int, default=0)
+    ap.add_argument("--sweep-splits", default="", help="comma list: one JSON line per split count (0 = the chooser)")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     a = ap.parse_args()
@@ -52,24 +53,27 @@ def main():
         n = int(nb[b]); tables[b, :n] = perm[o:o + n]; o += n
     tables, ctx_d = tables.to(dev), ctx.to(dev)
     lay = KvLayout.head_major(bs, Hkv, D) if a.layout == "head_major" else KvLayout.reference(bs, Hkv, D)
-    splits = a.splits
     out = torch.empty((B, H, D), dtype=torch.bfloat16, device=dev)
     ws = torch.empty(max(16, ops.paged_decode_workspace_bytes(B, H, D, 64)), dtype=torch.uint8, device=dev)
-    run = lambda: ops.paged_decode_attention(q, kc, vc, tables, ctx_d, lay, num_splits=splits, out=out, workspace=ws)
-    for _ in range(a.warmup):
-        run()
-    torch.cuda.synchronize()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.iters)]
-    for s, e in evs:
-        s.record(); run(); e.record()
-    torch.cuda.synchronize()
-    ms = sorted(s.elapsed_time(e) for s, e in evs)
-    med = ms[len(ms) // 2]
     alg = int((2 * ctx.long() * Hkv * D * 2).sum()) + 2 * B * H * D * 2 + 4 * int(nb.sum()) + 4 * B
-    print(json.dumps({"kernel": "paged_decode_attention", "cfg": os.environ.get("NVLLM_DECODE_CFG", "0"),
-                      "layout": a.layout, "batch": B, "ctx": L, "ragged": a.ragged, "heads": H, "kv_heads": Hkv,
-                      "splits": splits, "ms_median": round(med, 4), "ms_min": round(ms[0], 4),
-                      "alg_bytes": alg, "GBps_median": round(alg / med / 1e6, 1), "GBps_best": round(alg / ms[0] / 1e6, 1)}))
+    from nano_vllm_rs_b200 import _ffi
+    for splits in ([int(x) for x in a.sweep_splits.split(",")] if a.sweep_splits else [a.splits]):
+        run = lambda: ops.paged_decode_attention(q, kc, vc, tables, ctx_d, lay, num_splits=splits, out=out, workspace=ws)
+        for _ in range(a.warmup):
+            run()
+        torch.cuda.synchronize()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.iters)]
+        for s, e in evs:
+            s.record(); run(); e.record()
+        torch.cuda.synchronize()
+        ms = sorted(s.elapsed_time(e) for s, e in evs)
+        med = ms[len(ms) // 2]
+        chosen = splits or _ffi.lib().nvllm_paged_decode_choose_splits(B, H, Hkv, maxb * bs)
+        print(json.dumps({"kernel": "paged_decode_attention", "cfg": os.environ.get("NVLLM_DECODE_CFG", "0"),
+                          "layout": a.layout, "batch": B, "ctx": L, "ragged": a.ragged, "heads": H, "kv_heads": Hkv,
+                          "splits": splits, "splits_used": chosen, "ms_median": round(med, 4), "ms_min": round(ms[0], 4),
+                          "alg_bytes": alg, "GBps_median": round(alg / med / 1e6, 1), "GBps_best": round(alg / ms[0] / 1e6, 1)}),
+              flush=True)
 
 
 if __name__ == "__main__":
