@@ -8,9 +8,12 @@ from nano_vllm_rs_b200 import ops  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--only", default="", help="substring of the shape name")
     a = ap.parse_args()
     for name, B, L, H, Hkv in [("0.6B cfg2 prefill step", 64, 512, 16, 8), ("8B cfg3 prefill step", 32, 1024, 32, 8),
                                ("8B 4K prompt", 8, 4096, 32, 8), ("32B/TP8 32K", 1, 32768, 8, 1)]:
+        if a.only and a.only not in name:
+            continue
         D = 128
         q = torch.randn((B * L, H, D), device="cuda").to(torch.bfloat16)
         k = torch.randn((B * L, Hkv, D), device="cuda").to(torch.bfloat16)
