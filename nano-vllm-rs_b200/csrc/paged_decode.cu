@@ -25,6 +25,8 @@
 // Algorithmic bytes per launch: sum_b 2*L_b*Hkv*D*2 + 2*B*H*D*2 + 4*sum_b ceil(L_b/bs) + 4*B.
 #include <math.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace nvllm {
@@ -409,6 +411,248 @@ paged_decode_kernel(const DecodeParams p) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Persistent variant (one split): gridDim.x = min(items, resident CTAs) CTAs walk the (sequence, kv head, q group) items
+// round-robin, and every warp's cp.async pipeline runs ACROSS item boundaries: while the four warps merge their partial
+// states of item j and write its output, the first STAGES-1 sub-tiles of item j+1 are already in flight (its Q fragments
+// and context length were requested an item earlier).  The per-CTA ramp (launch, first table lookup, pipeline fill) and
+// drain of the one-CTA-per-item kernel — ~10 % of a 393 KB item at the cfg2 shape (769-token contexts) — are paid once
+// per CTA instead of once per item.  The merge buffer is separate from the pipeline buffers for that reason.
+template <int D, int STAGES, int NWARPS>
+__global__ void __launch_bounds__(NWARPS * 32, 2)
+paged_decode_persist_kernel(const DecodeParams p) {
+  using C = DecodeCfg<D, STAGES, NWARPS>;
+  constexpr int KS = D / 16;
+  constexpr int TILE = 16 * NWARPS;
+  extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int per_b = p.Hkv * p.ngrp;
+  const int items = p.batch * per_b;
+  const uint32_t warp_smem = smem_u32(smem) + warp * C::kWarpBytes;
+  float* so = reinterpret_cast<float*>(smem + C::kPipeBytes);  // [NWARPS][8][kOStride]
+  float* sml = so + NWARPS * 8 * C::kOStride;                  // [NWARPS][8][2]
+  pdl_wait();  // q and the newest KV row were written by the previous kernel
+
+  // ---- producer cursor (per warp): item, tile within it, and that item's metadata ---------------------------------
+  int p_it = blockIdx.x;          // item the next load belongs to
+  int p_t = 0, p_n = 0, p_ctx = 0;
+  const int32_t* p_table = nullptr;
+  const bf16* p_k = nullptr;
+  const bf16* p_v = nullptr;
+  int nxt_ctx = 0;                // context length of the item after p_it (requested one item ahead)
+  auto ctx_of = [&](int it) { return it < items ? __ldg(p.ctx + it / per_b) : 0; };
+  auto enter = [&](int ctx) {     // producer enters item p_it whose context length is ctx
+    if (p_it < items) {
+      const int b = p_it / per_b;
+      const int kvh = (p_it - b * per_b) / p.ngrp;
+      p_ctx = ctx;
+      p_n = (ctx + TILE - 1) / TILE;
+      p_table = p.tables + static_cast<int64_t>(b) * p.max_blocks;
+      p_k = p.kc + kvh * p.head_stride;
+      p_v = p.vc + kvh * p.head_stride;
+    } else {
+      p_n = 0;
+    }
+    p_t = 0;
+    nxt_ctx = ctx_of(p_it + gridDim.x);
+  };
+  enter(ctx_of(p_it));
+  int issued = 0;                 // groups committed so far (stage = issued % STAGES)
+  auto issue = [&]() {            // one commit group: the next sub-tile of this warp, or nothing when the work is done
+    while (p_it < items && p_t >= p_n) {  // skip to the next non-empty item
+      p_it += gridDim.x;
+      enter(nxt_ctx);
+    }
+    if (p_it < items) {
+      const int s = issued % STAGES;
+      const int tok_base = (p_t * NWARPS + warp) * 16;
+      int blk = -1, off = 0;
+      if (tok_base < p_ctx) {
+        const int bi = tok_base / p.block_size;
+        off = tok_base - bi * p.block_size;
+        if (bi < p.max_blocks) blk = __ldg(p_table + bi);
+      }
+      const uint32_t sK = warp_smem + s * C::kStageBytes;
+      const uint32_t sV = sK + C::kSubTileBytes;
+      const int c = lane % C::kChunks;
+      const int r0 = lane / C::kChunks;
+      const int64_t gofs0 = static_cast<int64_t>(blk < 0 ? 0 : blk) * p.blk_stride + c * 8;
+#pragma unroll
+      for (int j = 0; j < C::kRowsPerLane; ++j) {
+        const int r = r0 + j * C::kRowStep;
+        const bool valid = (blk >= 0) && (tok_base + r < p_ctx);
+        const int64_t gofs = valid ? gofs0 + static_cast<int64_t>(off + r) * p.tok_stride : 0;
+        const uint32_t dst = r * C::kRowBytes + ((c ^ (r & 7)) << 4);
+        cp_async_16(sK + dst, p_k + gofs, valid ? 16 : 0);
+        cp_async_16(sV + dst, p_v + gofs, valid ? 16 : 0);
+      }
+      ++p_t;
+    }
+    cp_async_commit();
+    ++issued;
+  };
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) issue();
+
+  // ---- Q^T B-fragments of an item (head n = lane/4, dims 16ks + 2(lane%4) + {0,1} (+8)) ---------------------------
+  auto load_q = [&](int it, uint32_t (&qf)[KS][2]) {
+    const int itc = it < items ? it : 0;
+    const int b = itc / per_b;
+    const int rem = itc - b * per_b;
+    const int kvh = rem / p.ngrp, grp = rem - kvh * p.ngrp;
+    const int gvalid = min(8, p.g - grp * 8);
+    const int hn = lane >> 2;
+    const bool hv = hn < gvalid && it < items;
+    const bf16* qrow = p.q + b * p.q_stride + static_cast<int64_t>(kvh * p.g + grp * 8 + (hv ? hn : 0)) * D;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int d0 = ks * 16 + (lane & 3) * 2;
+      qf[ks][0] = hv ? *reinterpret_cast<const uint32_t*>(qrow + d0) : 0u;
+      qf[ks][1] = hv ? *reinterpret_cast<const uint32_t*>(qrow + d0 + 8) : 0u;
+    }
+  };
+  uint32_t qb[KS][2], qn[KS][2];
+  load_q(blockIdx.x, qb);
+  int c_ctx = ctx_of(blockIdx.x);
+  int consumed = 0;  // sub-tiles consumed so far (stage = consumed % STAGES)
+
+  for (int it = blockIdx.x; it < items; it += gridDim.x) {
+    const int b = it / per_b;
+    const int rem = it - b * per_b;
+    const int kvh = rem / p.ngrp, grp = rem - kvh * p.ngrp;
+    const int gvalid = min(8, p.g - grp * 8);
+    const int qh0 = kvh * p.g + grp * 8;
+    const int ctx = c_ctx;
+    const int n = (ctx + TILE - 1) / TILE;
+    load_q(it + gridDim.x, qn);            // next item's Q and context length: needed an item from now
+    c_ctx = ctx_of(it + gridDim.x);
+
+    float m_run[2] = {-INFINITY, -INFINITY};
+    float l_run[2] = {0.f, 0.f};
+    float acc[KS][4];
+#pragma unroll
+    for (int mt = 0; mt < KS; ++mt) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0.f;
+
+    for (int i = 0; i < n; ++i) {
+      cp_async_wait<STAGES - 2>();
+      __syncwarp();
+      issue();
+      const uint32_t sK = warp_smem + (consumed % STAGES) * C::kStageBytes;
+      const uint32_t sV = sK + C::kSubTileBytes;
+      ++consumed;
+      const int tok_base = (i * NWARPS + warp) * 16;
+      const int mat = lane >> 3;
+      const int sw = lane & 7;
+      // ---- S^T = K . Q^T ------------------------------------------------------------------------
+      float sacc[4] = {0.f, 0.f, 0.f, 0.f};
+      {
+        const int r = sw + (mat & 1) * 8;
+        const uint32_t rowaddr = sK + r * C::kRowBytes;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          uint32_t a[4];
+          const int c = 2 * ks + (mat >> 1);
+          ldmatrix_x4(a, rowaddr + ((c ^ sw) << 4));
+          mma_bf16_16816(sacc, a, qb[ks][0], qb[ks][1]);
+        }
+      }
+      // ---- online softmax over tokens --------------------------------------------------------------
+      const int tokA = tok_base + (lane >> 2);
+      float s0 = sacc[0] * p.scale_log2, s1 = sacc[1] * p.scale_log2;
+      float s2 = sacc[2] * p.scale_log2, s3 = sacc[3] * p.scale_log2;
+      if (tokA >= ctx) s0 = s1 = -INFINITY;
+      if (tokA + 8 >= ctx) s2 = s3 = -INFINITY;
+      float mx0 = fmaxf(s0, s2), mx1 = fmaxf(s1, s3);
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, o));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, o));
+      }
+      const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+      const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0, ms1 = (mn1 == -INFINITY) ? 0.f : mn1;
+      const float corr0 = fast_exp2(m_run[0] - ms0), corr1 = fast_exp2(m_run[1] - ms1);
+      const float p0 = fast_exp2(s0 - ms0), p1 = fast_exp2(s1 - ms1);
+      const float p2 = fast_exp2(s2 - ms0), p3 = fast_exp2(s3 - ms1);
+      l_run[0] = l_run[0] * corr0 + p0 + p2;
+      l_run[1] = l_run[1] * corr1 + p1 + p3;
+      m_run[0] = mn0;
+      m_run[1] = mn1;
+      const uint32_t pb0 = movmatrix_trans(pack_bf16x2(p0, p1));
+      const uint32_t pb1 = movmatrix_trans(pack_bf16x2(p2, p3));
+      // ---- O^T += V^T . P^T -------------------------------------------------------------------------
+      {
+        const int r = sw + (mat >> 1) * 8;
+        const uint32_t rowaddr = sV + r * C::kRowBytes;
+        const bool rescale = __any_sync(0xffffffffu, (corr0 != 1.f) || (corr1 != 1.f));
+#pragma unroll
+        for (int mt = 0; mt < KS; ++mt) {
+          if (rescale) {
+            acc[mt][0] *= corr0;
+            acc[mt][1] *= corr1;
+            acc[mt][2] *= corr0;
+            acc[mt][3] *= corr1;
+          }
+          uint32_t a[4];
+          const int c = 2 * mt + (mat & 1);
+          ldmatrix_x4_trans(a, rowaddr + ((c ^ sw) << 4));
+          mma_bf16_16816(acc[mt], a, pb0, pb1);
+        }
+      }
+    }
+
+    // ---- merge the NWARPS partial states (the next item's sub-tiles keep arriving meanwhile) ----------------------
+#pragma unroll
+    for (int o = 4; o < 32; o <<= 1) {
+      l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], o);
+      l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], o);
+    }
+    {
+      const int h0 = (lane & 3) * 2;
+      float* sw_o = so + warp * 8 * C::kOStride;
+#pragma unroll
+      for (int mt = 0; mt < KS; ++mt) {
+        const int d = mt * 16 + (lane >> 2);
+        sw_o[h0 * C::kOStride + d] = acc[mt][0];
+        sw_o[(h0 + 1) * C::kOStride + d] = acc[mt][1];
+        sw_o[h0 * C::kOStride + d + 8] = acc[mt][2];
+        sw_o[(h0 + 1) * C::kOStride + d + 8] = acc[mt][3];
+      }
+      if (lane < 4) {
+        float* w_ml = sml + warp * 16;
+        w_ml[h0 * 2 + 0] = m_run[0];
+        w_ml[h0 * 2 + 1] = l_run[0];
+        w_ml[(h0 + 1) * 2 + 0] = m_run[1];
+        w_ml[(h0 + 1) * 2 + 1] = l_run[1];
+      }
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < gvalid * D; idx += NWARPS * 32) {
+      const int hn = idx / D;
+      const int d = idx - hn * D;
+      float M = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < NWARPS; ++w) M = fmaxf(M, sml[w * 16 + hn * 2]);
+      float o = 0.f, L = 0.f;
+      if (M != -INFINITY) {
+#pragma unroll
+        for (int w = 0; w < NWARPS; ++w) {
+          const float mw = sml[w * 16 + hn * 2];
+          const float f = (mw == -INFINITY) ? 0.f : fast_exp2(mw - M);
+          o += so[(w * 8 + hn) * C::kOStride + d] * f;
+          L += sml[w * 16 + hn * 2 + 1] * f;
+        }
+      }
+      p.out[b * p.out_stride + static_cast<int64_t>(qh0 + hn) * D + d] = __float2bfloat16_rn(L > 0.f ? o / L : 0.f);
+    }
+    __syncthreads();  // the merge buffer is free again
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) { qb[ks][0] = qn[ks][0]; qb[ks][1] = qn[ks][1]; }
+  }
+  cp_async_wait<0>();
+}
+
 // Combines the split-K partials: grid (H, B), D threads.
 template <int D>
 __global__ void __launch_bounds__(D) paged_decode_reduce_kernel(const DecodeParams p) {
@@ -448,6 +692,25 @@ static int launch_decode(const DecodeParams& p, cudaStream_t stream) {
   NVLLM_CUDA(launch_pdl(kern, grid, dim3(NWARPS * 32), kBytes, stream, p));
   if (p.num_splits > 1)
     NVLLM_CUDA(launch_pdl(paged_decode_reduce_kernel<D>, dim3(p.H, p.batch), dim3(D), 0, stream, p));
+  return 0;
+}
+
+template <int D, int STAGES, int NWARPS>
+static int launch_decode_persist(const DecodeParams& p, cudaStream_t stream) {
+  using C = DecodeCfg<D, STAGES, NWARPS>;
+  auto kern = paged_decode_persist_kernel<D, STAGES, NWARPS>;
+  constexpr int kBytes = C::kPipeBytes + C::kMergeBytes;
+  NVLLM_SMEM_ATTR_ONCE(kern, kBytes);
+  static std::atomic<int> per_sm_cached{0};
+  int per_sm = per_sm_cached.load(std::memory_order_relaxed);
+  if (per_sm == 0) {
+    NVLLM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NWARPS * 32, kBytes));
+    if (per_sm < 1) per_sm = 1;
+    per_sm_cached.store(per_sm, std::memory_order_relaxed);
+  }
+  const long items = static_cast<long>(p.batch) * p.Hkv * p.ngrp;
+  const long slots = static_cast<long>(per_sm) * sm_count();
+  NVLLM_CUDA(launch_pdl(kern, dim3(static_cast<unsigned>(items < slots ? items : slots)), dim3(NWARPS * 32), kBytes, stream, p));
   return 0;
 }
 
@@ -575,6 +838,10 @@ static int decode_dispatch(void* out, const void* q, void* k_cache, void* v_cach
   p.scale_log2 = scale * 1.4426950408889634f;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (fuse) return launch_decode<128, 3, 4, true>(p, st);
+  // One split and more items than resident CTAs: the persistent kernel (NVLLM_DECODE_PERSIST=0: one CTA per item).
+  if (D == 128 && num_splits == 1 && knobs().decode_persist && decode_cfg_id() == 0 &&
+      static_cast<long>(batch) * Hkv * p.ngrp > 2L * sm_count())
+    return launch_decode_persist<128, 3, 4>(p, st);
   if (D == 128) {
     switch (decode_cfg_id()) {
       case 1: return launch_decode<128, 4, 4>(p, st);

@@ -77,6 +77,42 @@ def test_paged_decode_attention_vs_oracle(cuda, kind, case):
     assert_close(to_np_f32(out), ref, ATT_ATOL, ATT_RTOL, f"paged decode {case}")
 
 
+PERSIST_CASES = [
+    # (batch, max_ctx, H, Hkv, block_size): more (sequence, kv head, group) items than resident CTAs -> the persistent kernel
+    (80, 700, 16, 8, 256),      # 640 items, Qwen3-0.6B heads, ragged contexts incl. empty rows
+    (330, 300, 4, 1, 256),      # TP=8 shard shape (one kv head per rank, group 4): 330 items on 296 CTAs
+    (50, 260, 24, 2, 16),       # group 12: two q-head groups per kv head (200 items... x ngrp 2 = 200), block size 16
+    (700, 90, 8, 8, 32),        # many short items: item boundaries dominate
+]
+
+
+@pytest.mark.parametrize("kind", ["reference", "head_major"])
+@pytest.mark.parametrize("case", PERSIST_CASES, ids=[str(i) for i in range(len(PERSIST_CASES))])
+def test_paged_decode_persistent_kernel(cuda, kind, case, monkeypatch):
+    """The persistent variant of K2 (pipelines run across item boundaries) vs the oracle, and bit-identical to the
+    one-CTA-per-item kernel (same per-warp token order, same merge).  Ragged contexts with empty rows (padded graph rows)."""
+    from nano_vllm_rs_b200 import ops
+    B, L, H, Hkv, bs = case
+    D = 128
+    rng = np.random.default_rng(B * 7 + L)
+    ctx = rng.integers(1, L + 1, B).tolist()
+    for i in range(0, B, 17):
+        ctx[i] = 0                                     # empty rows anywhere in the item sequence
+    ctx[-1] = L
+    kc, vc, tables, _, _ = make_paged_kv(rng, ctx, bs, Hkv, D)
+    q = randn_bf16(rng, (B, H, D))
+    scale = 1.0 / np.sqrt(D)
+    args = (to_dev_bf16(q, cuda), cache_to_layout(kc, kind, cuda), cache_to_layout(vc, kind, cuda),
+            torch.from_numpy(tables).to(cuda), torch.tensor(ctx, dtype=torch.int32, device=cuda), _layout(kind, bs, Hkv, D))
+    out = ops.paged_decode_attention(*args, scale=scale, num_splits=1)
+    monkeypatch.setenv("NVLLM_DECODE_PERSIST", "0")
+    plain = ops.paged_decode_attention(*args, scale=scale, num_splits=1)
+    torch.cuda.synchronize()
+    assert torch.equal(out, plain)
+    ref = O.flash_attention_decode(q, kc, vc, tables, np.asarray(ctx, np.int32), scale)
+    assert_close(to_np_f32(out), ref, ATT_ATOL, ATT_RTOL, f"persistent paged decode {case}")
+
+
 FUSED_CASES = [
     # (context_lens INCLUDING this step's token, H, Hkv, block_size, num_splits, qk_norm)
     ([1], 16, 8, 256, 1, True),                             # nothing cached: the step's own token only
