@@ -55,7 +55,7 @@ static void parse_knobs() {
   k.profile = num("NVLLM_PROFILE", 0);
   k.ar_ll = num("NVLLM_AR_LL", 1);
   k.gemm_push = num("NVLLM_GEMM_PUSH", 0);
-  k.decode_persist = num("NVLLM_DECODE_PERSIST", 1);
+  k.decode_persist = num("NVLLM_DECODE_PERSIST", 0);
   if (const char* e = getenv("NVLLM_AR_LL_MAX_BYTES")) { const long long v = atoll(e); if (v >= 0 && v <= (1ll << 30)) k.ar_ll_max_bytes = v; }
   if (const char* e = getenv("NVLLM_COMM_TIMEOUT_MS")) { const long long v = atoll(e); if (v > 0) k.comm_timeout_ms = v; }
   g_knobs = k;

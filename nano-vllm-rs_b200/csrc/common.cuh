@@ -63,7 +63,7 @@ struct Knobs {
   int fuse_rope = 0;        // NVLLM_FUSE_ROPE: qkv GEMM epilogue with q/k-norm + RoPE + KV store
   int fuse_decode = 0;      // NVLLM_FUSE_DECODE: 1 = q/k-norm + RoPE + KV store inside the paged decode attention (first version measured 9 % slower)
   int fused_tp = 1;         // NVLLM_FUSED_TP: 0 = ncclAllReduce + separate add_rmsnorm
-  int decode_persist = 1;   // NVLLM_DECODE_PERSIST: 0 = one CTA per (sequence, kv head, group) item instead of the persistent kernel
+  int decode_persist = 0;   // NVLLM_DECODE_PERSIST: 1 = persistent paged decode kernel (pipelines across item boundaries; measured +-1 %: no gain)
   int gemm_push = 0;        // NVLLM_GEMM_PUSH: 1 = o_proj / down_proj push foreign rows from their epilogue (16-byte NVLink packets: measured 2.8 % slower at N=2)
   int ar_ll = 1;            // NVLLM_AR_LL: 0 = always the flag-protocol fused all-reduce (no low-latency push variant)
   long long ar_ll_max_bytes = 8ll << 20;  // NVLLM_AR_LL_MAX_BYTES: largest message of the low-latency variant (6x this is reserved)
