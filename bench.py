@@ -674,8 +674,19 @@ def run_prefix(args, rank, world, local):
     return line, ok_blocks
 
 
+def arm_watchdog():
+    """A bench run that stops making progress (a rank waiting for a peer that died, a kernel that never returns) must not
+    sit there until someone else's limit kills it without a trace: after BENCH_WATCHDOG_S seconds (default 20 min; a normal
+    run takes 1-3) every thread's Python stack goes to stderr and the process exits with a non-zero status."""
+    import faulthandler
+    limit = float(os.environ.get("BENCH_WATCHDOG_S", "1200"))
+    if limit > 0:
+        faulthandler.dump_traceback_later(limit, exit=True)
+
+
 def main():
     args = parse()
+    arm_watchdog()
     if args.impl == "reference":
         return reference_arm(args)
     import torch
