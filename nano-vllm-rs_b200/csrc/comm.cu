@@ -412,8 +412,9 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
       }
       if (!dead) {
         // Re-poll in ROUNDS: every vector that has not arrived is re-loaded in the same round (all in flight together), so
-        // a round costs one L2 round trip however many of the KCH x (WORLD-1) vectors are still missing.  (Spinning on
-        // them one after the other cost up to 14 round trips per thread at 8 ranks: 14.4 us per call instead of 8.4.)
+        // a round costs one L2 round trip however many of the KCH x (WORLD-1) vectors are still missing (spinning on them
+        // one after the other could cost up to 14 round trips per thread at 8 ranks; measured it made no difference on an
+        // idle box — 14.4 us per 640 KiB call either way, profiles/r02_scaling.md — but it bounds the worst case).
         long long t0 = 0;
         while (true) {
           bool miss = false;
