@@ -77,6 +77,14 @@ def tensor_peak():
         return 1590.0, "fallback"
 
 
+_T0 = time.time()
+
+
+def progress(msg):
+    """One timestamped line per phase on stderr (every rank): when a run stalls, the last line says where."""
+    print(f"[bench rank {os.environ.get('RANK', '0')} +{time.time() - _T0:6.1f}s] {msg}", file=sys.stderr, flush=True)
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -422,7 +430,9 @@ def run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity, w
                    max_model_len=max(4096, ((max_len + 255) // 256) * 256), enforce_eager=eager,
                    max_position_embeddings=max(40960, ((max_len + 255) // 256) * 256))
     seed, std = 1234, 0.02
+    progress(f"building the engine: {model}, tp={world}, {B} sequences, {nblk} KV blocks")
     eng = E.LLMEngine(cfg, comm=comm, seed=seed, std=std)
+    progress("engine ready (weights initialised, KV cache allocated); prefilling")
     rng = np.random.default_rng(1234)                      # token stream seed 1234, ids mod vocab
     sp = E.SamplingParams(temperature=0.0, max_tokens=W + 2 * K + 64, ignore_eos=True)
     sids = [eng.add_request(rng.integers(0, cfg.vocab_size, prompt), sp) for _ in range(B)]
@@ -457,6 +467,7 @@ def run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity, w
         eng.step(); n_prefill += 1
     torch.cuda.synchronize()
     prefill_s = time.perf_counter() - t0
+    progress(f"prefill done: {n_prefill} steps in {prefill_s:.1f} s; warm-up decode steps")
     agree_steps, agree = 0, True
     if world > 1 and want_parity:
         agree &= ranks_agree_on_last_tokens(); agree_steps += 1            # the prefill's sampled tokens
@@ -466,6 +477,7 @@ def run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity, w
             agree &= ranks_agree_on_last_tokens(); agree_steps += 1
     torch.cuda.synchronize()
 
+    progress("warm-up done (decode graph captured); timing")
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -709,7 +721,9 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         if not args.no_parity:
+            progress("process group up; tp_parity check (seeded tiny model vs the TP=1 oracle)")
             tp_parity = tp_parity_check(E, _ffi, lib, rank, world, torch)
+            progress(f"tp_parity done: ok={tp_parity['ok']}")
     model, wl, prompt, K, W = workload(args)
     line = run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity=not args.no_parity,
                       want_cpu=not args.no_cpu_baseline)
