@@ -98,6 +98,35 @@ int nvllm_paged_decode_attention(void* out, const void* q, const void* k_cache, 
                                  size_t workspace_bytes, int32_t num_splits, int32_t dtype,
                                  void* stream);
 
+/* nvllm_paged_decode_attention for callers that cannot provide a workspace.  NO COUNTERPART IN THE REFERENCE (its
+ * decode attention is candle tensor ops that allocate freely); this exists for integrations, not for parity.
+ *
+ * Who needs it: a caller that sits where device memory cannot be obtained — an operator hook or host callback that is
+ * handed only the tensors of one op, an embedder whose memory pool is fixed once serving starts, a C / Rust host with
+ * no CUDA allocator of its own.  It still passes q, the caches, the tables and `out`; the f32 split-K partials go to an
+ * array built into libnvllm.so's device image.  The call performs no cudaMalloc / cudaFree and calls no allocating
+ * library routine.  Same arguments, kernels and results as nvllm_paged_decode_attention (bit for bit at an equal
+ * num_splits), minus `workspace` / `workspace_bytes`.
+ *
+ * Limits and rules:
+ *   - the array is nvllm_paged_decode_static_scratch_bytes() = 8 MiB, present on EVERY GPU that loads the library until
+ *     the process exits.  A call that needs more — nvllm_paged_decode_workspace_bytes(batch, num_heads, head_dim,
+ *     num_splits) > 8 MiB; num_splits = 0 resolves through nvllm_paged_decode_choose_splits first — returns
+ *     NVLLM_ERR_WORKSPACE with the sizes in nvllm_last_error() and launches nothing.  One split needs no scratch at all.
+ *   - the first call on each device looks up that device's address of the array (cudaGetSymbolAddress, with the calling
+ *     thread's current device, which must be the device of `stream` and of every buffer) and remembers it.  Make that
+ *     first call during set-up, before any CUDA stream capture begins.
+ *   - all calls on a GPU share the one array.  Calls ordered on one stream are safe; calls that can overlap on the GPU
+ *     (two streams, or two threads with a stream each) race on the partials and return garbage — serialise them or use
+ *     the workspace variant.  The array keeps whatever the last call left; nothing needs clearing, because every
+ *     partial a call reads was written by that same call. */
+size_t nvllm_paged_decode_static_scratch_bytes(void);
+int nvllm_paged_decode_attention_static(void* out, const void* q, const void* k_cache, const void* v_cache,
+                                        const int32_t* block_tables, const int32_t* context_lens, int32_t batch,
+                                        int32_t num_heads, int32_t max_blocks_per_seq, int64_t q_token_stride,
+                                        int64_t out_token_stride, const nvllm_kv_layout* layout, float scale,
+                                        int32_t num_splits, int32_t dtype, void* stream);
+
 /* K7 + K1 + K2 in ONE launch for decode steps — replaces, per layer, what Qwen3Attention::forward does between qkv_proj
  * and o_proj (src/models/qwen3.rs:219-233): per-head q/k RMSNorm + RotaryEmbedding::forward
  * (src/layers/rotary_embedding.rs:23-48,145-158), Attention::store_kv_cache (src/layers/attention.rs:150-174) and

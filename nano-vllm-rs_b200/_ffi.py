@@ -44,6 +44,8 @@ PROTOTYPES = {
     "nvllm_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "nvllm_paged_decode_choose_splits": (i32, [i32, i32, i32, i32]),
     "nvllm_paged_decode_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64, LP, f32, vp, sz, i32, i32, vp]),
+    "nvllm_paged_decode_static_scratch_bytes": (sz, []),
+    "nvllm_paged_decode_attention_static": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64, LP, f32, i32, i32, vp]),
     "nvllm_paged_decode_attention_fused": (i32, [vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, vp, vp, i32, i32, i32, i64, i64,
                                                  LP, f32, vp, sz, i32, i32, vp]),
     "nvllm_varlen_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64,

@@ -886,3 +886,70 @@ extern "C" int nvllm_paged_decode_attention_fused(void* out, const void* qkv, co
                                 qkv_token_stride, out_token_stride, layout, scale, workspace, workspace_bytes, num_splits, dtype,
                                 stream, fa);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Split-K decode attention for callers that cannot hand us a workspace.
+//
+// Who this is for: code that reaches the library from a place where device memory cannot be obtained —
+// a host callback or plugin hook that only receives the tensors of one operator, a runtime whose memory pool
+// is frozen once serving starts, a C or Rust embedder without a CUDA allocator of its own.  Such a caller has its
+// inputs and its output and nothing else, yet the split-K path needs somewhere to park the f32 partial sums between
+// its two launches.  The array below is that place: it lives in the library's own device image, so it exists on
+// every GPU that loads libnvllm.so from the moment the module is loaded until the process ends, and nobody has to
+// allocate or free it.
+//
+// The price, stated once: kStaticScratchBytes (8 MiB) of HBM per GPU for the life of the process; one array per
+// GPU shared by every call, so two calls that may run at the same time on one GPU (different streams, or
+// different host threads on different streams) overwrite each other's partials; and a hard size limit.
+// ------------------------------------------------------------------------------------------------
+namespace nvllm {
+constexpr size_t kStaticScratchBytes = size_t(8) << 20;
+constexpr int kStaticScratchMaxDevices = 64;
+static __device__ __align__(256) float g_decode_static_scratch[kStaticScratchBytes / sizeof(float)];
+
+// In host code `g_decode_static_scratch` is only a handle the runtime uses to look the array up; its value is not a
+// device address.  The real address differs per GPU, so it is asked for once per device, with that device current.
+static int decode_static_scratch_ptr(float** out) {
+  static std::atomic<float*> per_device[kStaticScratchMaxDevices];
+  int dev = -1;
+  NVLLM_CUDA(cudaGetDevice(&dev));
+  NVLLM_CHECK_ARG(dev >= 0 && dev < kStaticScratchMaxDevices, NVLLM_ERR_ARG,
+                  "paged_decode_static: device ordinal %d outside [0, %d)", dev, kStaticScratchMaxDevices);
+  float* ptr = per_device[dev].load(std::memory_order_acquire);
+  if (ptr == nullptr) {
+    void* sym = nullptr;
+    NVLLM_CUDA(cudaGetSymbolAddress(&sym, g_decode_static_scratch));
+    NVLLM_CHECK_ARG(sym != nullptr, NVLLM_ERR_STATE, "paged_decode_static: cudaGetSymbolAddress returned NULL on device %d", dev);
+    ptr = static_cast<float*>(sym);
+    per_device[dev].store(ptr, std::memory_order_release);  // two threads racing here store the same address
+  }
+  *out = ptr;
+  return 0;
+}
+}  // namespace nvllm
+
+extern "C" size_t nvllm_paged_decode_static_scratch_bytes(void) { return nvllm::kStaticScratchBytes; }
+
+extern "C" int nvllm_paged_decode_attention_static(void* out, const void* q, const void* k_cache, const void* v_cache,
+                                                   const int32_t* block_tables, const int32_t* context_lens,
+                                                   int32_t batch, int32_t num_heads, int32_t max_blocks_per_seq,
+                                                   int64_t q_token_stride, int64_t out_token_stride,
+                                                   const nvllm_kv_layout* layout, float scale, int32_t num_splits,
+                                                   int32_t dtype, void* stream) {
+  NVLLM_CHECK_ARG(layout != nullptr, NVLLM_ERR_ARG, "paged_decode_static: layout is NULL");
+  if (num_splits <= 0)
+    num_splits = nvllm_paged_decode_choose_splits(batch, num_heads, layout->num_kv_heads,
+                                                  max_blocks_per_seq * layout->block_size);
+  const size_t need = nvllm_paged_decode_workspace_bytes(batch, num_heads, layout->head_dim, num_splits);
+  NVLLM_CHECK_ARG(need <= nvllm::kStaticScratchBytes, NVLLM_ERR_WORKSPACE,
+                  "paged_decode_static: batch %d x heads %d x splits %d x head_dim %d needs %zu bytes of partials, the "
+                  "built-in scratch holds %zu; use fewer splits or nvllm_paged_decode_attention with your own workspace",
+                  batch, num_heads, num_splits, layout->head_dim, need, nvllm::kStaticScratchBytes);
+  float* scratch = nullptr;
+  if (int rc = nvllm::decode_static_scratch_ptr(&scratch)) return rc;
+  // Nothing has to be cleared: the first launch writes every (sequence, head, split) partial the second one reads,
+  // empty splits included (m = -inf, l = 0), so what an earlier call left behind is never looked at.
+  return nvllm::decode_dispatch(out, q, const_cast<void*>(k_cache), const_cast<void*>(v_cache), block_tables, context_lens,
+                                batch, num_heads, max_blocks_per_seq, q_token_stride, out_token_stride, layout, scale,
+                                scratch, nvllm::kStaticScratchBytes, num_splits, dtype, stream, nvllm::FuseArgs{});
+}
