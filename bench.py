@@ -80,8 +80,13 @@ def tensor_peak():
 _T0 = time.time()
 
 
+_LAST = {"t": time.time(), "msg": "start"}
+
+
 def progress(msg):
-    """One timestamped line per phase on stderr (every rank): when a run stalls, the last line says where."""
+    """One timestamped line per phase on stderr (every rank): when a run stalls, the last line says where.  Every call
+    also feeds the stall watchdog (arm_watchdog)."""
+    _LAST["t"], _LAST["msg"] = time.time(), msg
     print(f"[bench rank {os.environ.get('RANK', '0')} +{time.time() - _T0:6.1f}s] {msg}", file=sys.stderr, flush=True)
 
 
@@ -333,9 +338,11 @@ def tp_parity_check(E, _ffi, lib, rank, world, torch):
         layers = ocfg["num_hidden_layers"]
     res = dict(vs="oracle (TP=1 numpy restatement, same seeded weights)", arch=arch, world=world, steps=0, decode_steps=0,
                rows=0, strict_tokens=0, near_ties=0, max_err_sigma=0.0, ranks_agree=True, ok=True, why="")
+    progress("tp_parity: communicator + runner up, stepping")
     while not sched.is_finished():
         b = sched.schedule()
         toks, logits = runner.execute_model(b, return_logits=True)
+        progress(f"tp_parity: step {res['steps']} executed; gathering logits")
         lg = torch.from_numpy(np.ascontiguousarray(logits)).cuda()
         tk = torch.from_numpy(np.ascontiguousarray(toks)).cuda()
         all_lg = [torch.empty_like(lg) for _ in range(world)]
@@ -373,6 +380,7 @@ def tp_parity_check(E, _ffi, lib, rank, world, torch):
     dist.broadcast(flag, 0)
     res["ok"] = bool(flag.item())
     dist.barrier()
+    progress("tp_parity: destroying its runner and communicator")
     del runner, sched
     _ffi.check(lib.nvllm_comm_destroy(comm))
     return res
@@ -494,6 +502,7 @@ def run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity, w
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     torch.cuda.cudart().cudaProfilerStop()
+    progress(f"e2e region done ({K} steps through LLEngine.step); device-timed replays")
     barrier()
     launch_profile = None
     if args.profile:
@@ -517,9 +526,11 @@ def run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity, w
     clocks = sampler.stop() if rank == 0 else None
     layers, cap = cfg.num_hidden_layers, cfg.max_model_len // 256
     barrier()
+    progress("measurements done; tearing the engine down")
     del eng
     if comm is not None:
         _ffi.check(lib.nvllm_comm_destroy(comm))
+    progress("engine and communicator destroyed")
     if rank != 0:
         return None
     peak, peak_src = peaks()
@@ -569,6 +580,7 @@ def run_decode(args, model, wl, prompt, K, W, rank, world, local, want_parity, w
         line["launch_profile"] = launch_profile
     if world == 1 and want_cpu:
         ctx_mid = (ctx_first + ctx_last) // 2
+        progress("cpu_baseline: the numpy oracle on a bounded sample")
         tps, cores, desc, _ = cpu_decode_sample(model, ctx_mid, 16, 2, 1)
         line["cpu_baseline"] = {"value": round(tps, 2), "unit": "tokens/s", "cores": cores, "kind": "port", "sample": desc}
     return line
@@ -688,12 +700,33 @@ def run_prefix(args, rank, world, local):
 
 def arm_watchdog():
     """A bench run that stops making progress (a rank waiting for a peer that died, a kernel that never returns) must not
-    sit there until someone else's limit kills it without a trace: after BENCH_WATCHDOG_S seconds (default 20 min; a normal
-    run takes 1-3) every thread's Python stack goes to stderr and the process exits with a non-zero status."""
+    sit there until someone else's limit kills it without a trace.  A daemon thread watches the time since the last
+    progress() line: once one PHASE has lasted BENCH_WATCHDOG_S seconds (default 240; a whole normal run takes 40-60 s) it
+    dumps every thread's Python stack to stderr, prints {"error": "watchdog", "phase": ...} as this process's JSON line on
+    stdout — so the record names the phase even when stderr's tail is lost — and exits with status 3 (torchrun then stops
+    the other ranks).  ctypes calls and torch's CUDA waits release the GIL, so the thread runs while the main thread is
+    stuck in either; faulthandler's C-level timer 30 s later is the backstop for a stall that holds the GIL."""
     import faulthandler
-    limit = float(os.environ.get("BENCH_WATCHDOG_S", "1200"))
-    if limit > 0:
-        faulthandler.dump_traceback_later(limit, exit=True)
+    import threading
+    limit = float(os.environ.get("BENCH_WATCHDOG_S", "240"))
+    if limit <= 0:
+        return
+
+    def watch():
+        while True:
+            time.sleep(1.0)
+            stalled = time.time() - _LAST["t"]
+            if stalled > limit:
+                faulthandler.dump_traceback(file=sys.stderr, all_threads=True)
+                print(json.dumps({"error": "watchdog", "phase": _LAST["msg"], "stalled_s": round(stalled, 1),
+                                  "rank": int(os.environ.get("RANK", "0")), "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+                                  "since_start_s": round(time.time() - _T0, 1)}), flush=True)
+                sys.stderr.flush()
+                os._exit(3)
+            faulthandler.cancel_dump_traceback_later()
+            faulthandler.dump_traceback_later(max(1.0, limit + 30.0 - stalled), exit=True)
+
+    threading.Thread(target=watch, name="bench-watchdog", daemon=True).start()
 
 
 def main():
@@ -731,6 +764,7 @@ def main():
     if rank == 0:
         if world == 1:
             pk, _ = tensor_peak()
+            progress("tensor_kernels: prefill GEMM / attention micro-measurements")
             line["tensor_kernels"] = tensor_kernels(pk)
             ok = line.get("parity", {}).get("ok", True)
         else:

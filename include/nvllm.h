@@ -282,6 +282,10 @@ int nvllm_sample(int64_t* out_ids, const float* logits, int32_t batch, int32_t v
 typedef struct nvllm_comm nvllm_comm;
 int nvllm_comm_unique_id(void* h_id_out);
 int nvllm_comm_init(nvllm_comm** comm, const void* h_id, int32_t rank, int32_t world);
+/* Collective tear-down: closes the peer mappings, meets the other ranks once more (an all-reduce of a scratch word, with a
+ * host-side deadline of 6 x NVLLM_COMM_TIMEOUT_MS) so nobody frees a region a peer still has mapped, then frees.  When the
+ * communicator has already reported NVLLM_ERR_COMM, or the meeting times out, it does NOT wait: the region is leaked, the
+ * NCCL communicator aborted, and NVLLM_ERR_COMM returned — a dead peer can never keep this call from returning. */
 int nvllm_comm_destroy(nvllm_comm* comm);
 /* In-place sum over ranks of buf[count] (bf16 or f32), enqueued on `stream` (graph-capturable). */
 int nvllm_allreduce(nvllm_comm* comm, void* buf, size_t count, int32_t dtype, void* stream);

@@ -8,6 +8,8 @@
 #include <string.h>
 
 #include <atomic>
+#include <chrono>
+#include <thread>
 
 #include "common.cuh"
 
@@ -25,6 +27,7 @@ struct NcclApi {
   int (*GetUniqueId)(ncclUniqueId*) = nullptr;
   int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*CommAbort)(ncclComm_t) = nullptr;  // optional
   int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
   int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
@@ -51,6 +54,7 @@ static NcclApi& nccl() {
   NVLLM_SYM(GetUniqueId, "ncclGetUniqueId");
   NVLLM_SYM(CommInitRank, "ncclCommInitRank");
   NVLLM_SYM(CommDestroy, "ncclCommDestroy");
+  NVLLM_SYM(CommAbort, "ncclCommAbort");
   NVLLM_SYM(AllReduce, "ncclAllReduce");
   NVLLM_SYM(AllGather, "ncclAllGather");
   NVLLM_SYM(GetErrorString, "ncclGetErrorString");
@@ -63,6 +67,28 @@ static int nccl_status(int rc, const char* what) {
   if (rc == ncclSuccess) return 0;
   set_error("%s: NCCL error %d (%s)", what, rc, nccl().GetErrorString ? nccl().GetErrorString(rc) : "?");
   return NVLLM_ERR_COMM;
+}
+
+
+// Host-side deadline for work this library enqueued on a stream of its own (the NCCL collectives of set-up and
+// tear-down): an NCCL kernel waiting for a rank that never joins has no timeout of its own and would keep the host in
+// cudaStreamSynchronize for ever.  0 = finished, NVLLM_ERR_COMM = still running after 6 x NVLLM_COMM_TIMEOUT_MS (ranks reach
+// set-up and tear-down less in step than they reach a decode step; the stream is left as it is: the caller must not free
+// what the kernel may still touch), > 0 = cudaError_t.
+static int stream_wait_bounded(cudaStream_t st, const char* what) {
+  const auto t0 = std::chrono::steady_clock::now();
+  const long long limit_ms = 6 * knobs().comm_timeout_ms;
+  for (int spins = 0;; ++spins) {
+    const cudaError_t e = cudaStreamQuery(st);
+    if (e == cudaSuccess) return 0;
+    if (e != cudaErrorNotReady) return cuda_status(e, what);
+    const long long ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+    if (ms > limit_ms) {
+      set_error("%s: still running after %lld ms (6 x NVLLM_COMM_TIMEOUT_MS) - a peer rank never joined the collective", what, ms);
+      return NVLLM_ERR_COMM;
+    }
+    if (spins > 2000) std::this_thread::sleep_for(std::chrono::microseconds(200));
+  }
 }
 
 }  // namespace nvllm
@@ -107,17 +133,26 @@ __device__ __forceinline__ uint4 ld_sys_16(const void* p) {
                : "memory");
   return r;
 }
+// What a kernel that gave up was waiting for, for nvllm_comm_error's message.  err[] is host-mapped: [0] sticky flag,
+// [1] phase (1 / 2 = flag protocol waiting for ready / done, 3 = low-latency reduce waiting for staged partial rows,
+// 4 = low-latency gather waiting for normed rows), [2] row (or the peer whose flag is missing), [3] CTA, [4] epoch or
+// buffer pair, [5] bit mask of the source ranks still missing (phase 3).  Several threads may report: any one wins.
+__device__ __forceinline__ void report_timeout(int* err, int phase, int what, int aux, int mask) {
+  volatile int* e = err;
+  if (e[0] == 0) { e[1] = phase; e[2] = what; e[3] = static_cast<int>(blockIdx.x); e[4] = aux; e[5] = mask; }
+  e[0] = 1;
+}
 // Spins until *p reaches `target` (wrap-safe).  A peer that never arrives (crashed rank, a host-side stall longer than
 // NVLLM_COMM_TIMEOUT_MS) must neither hang the GPU nor poison the CUDA context: the kernel raises the host-visible error
 // flag, marks the communicator dead (later calls stop waiting) and runs to completion; the host reports NVLLM_ERR_COMM.
 __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t target, long long timeout_cycles, uint32_t* dead,
-                                          int* err) {
+                                          int* err, int phase = 1) {
   if (static_cast<int32_t>(ld_acquire_sys(p) - target) >= 0) return;
   const long long t0 = clock64();
   while (static_cast<int32_t>(ld_acquire_sys(p) - target) < 0) {
     if (clock64() - t0 > timeout_cycles) {
       *reinterpret_cast<volatile uint32_t*>(dead) = 1u;
-      *reinterpret_cast<volatile int*>(err) = 1;
+      report_timeout(err, phase, static_cast<int>(threadIdx.x), static_cast<int>(target), 0);
       __threadfence_system();
       return;
     }
@@ -257,7 +292,7 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
   if (s_last) {
     if (threadIdx.x < WORLD) {
       st_release_sys(reinterpret_cast<uint32_t*>(peer_of(p, threadIdx.x)) + 64 + p.rank, epoch);  // done[rank] on peer
-      if (!dead) wait_flag(ctrl + 64 + threadIdx.x, epoch, p.timeout_cycles, ctrl + 130, p.err);
+      if (!dead) wait_flag(ctrl + 64 + threadIdx.x, epoch, p.timeout_cycles, ctrl + 130, p.err, 2);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -427,7 +462,13 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
           if (t0 == 0) t0 = clock64();
           if (clock64() - t0 > p.timeout_cycles || *reinterpret_cast<volatile uint32_t*>(dead_p) != 0) {
             *reinterpret_cast<volatile uint32_t*>(dead_p) = 1u;
-            *reinterpret_cast<volatile int*>(p.err) = 1;
+            int missing = 0;
+#pragma unroll
+            for (int k = 0; k < KCH; ++k)
+#pragma unroll
+              for (int q = 0; q < WORLD; ++q)
+                if (q != p.rank && threadIdx.x + (k0 + k) * blockDim.x < nvec && !ll_arrived(a[k][q])) missing |= 1 << q;
+            report_timeout(p.err, 3, row, static_cast<int>(b), missing);
             __threadfence_system();
             break;
           }
@@ -518,7 +559,7 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
         if (t0 == 0) t0 = clock64();
         if (clock64() - t0 > p.timeout_cycles || *reinterpret_cast<volatile uint32_t*>(dead_p) != 0) {
           *reinterpret_cast<volatile uint32_t*>(dead_p) = 1u;
-          *reinterpret_cast<volatile int*>(p.err) = 1;
+          report_timeout(p.err, 4, row, static_cast<int>(b), 0);
           __threadfence_system();
           break;
         }
@@ -651,43 +692,66 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base) {
   const size_t user_off = kSymCtrlBytes + 6 * ll_cap;
   const size_t total = user_off + ((bytes + 255) & ~static_cast<size_t>(255));
   void* base = nullptr;
-  NVLLM_CUDA(cudaMalloc(&base, total));
-  NVLLM_CUDA(cudaMemset(base, 0, total));
+  cudaIpcMemHandle_t* d_all = nullptr;
+  cudaStream_t st = nullptr;
+  bool stream_busy = false;  // a collective that never finished may still write d_all: leak it rather than free it
+  // Every early exit below releases what was taken so far (base, d_all and the opened peer mappings leaked).
+  auto fail = [&](int rc) {
+    for (int r = 0; r < comm->world; ++r) {
+      if (r != comm->rank && comm->sym_peer[r]) cudaIpcCloseMemHandle(comm->sym_peer[r]);
+      comm->sym_peer[r] = nullptr;
+    }
+    if (!stream_busy) {
+      if (st) cudaStreamDestroy(st);
+      if (d_all) cudaFree(d_all);
+      if (base) cudaFree(base);
+    }
+    return rc;
+  };
+#define NVLLM_CUDA_OR_FAIL(expr)                                       \
+  do {                                                                 \
+    cudaError_t _e = (expr);                                           \
+    if (_e != cudaSuccess) return fail(::nvllm::cuda_status(_e, #expr)); \
+  } while (0)
+  NVLLM_CUDA_OR_FAIL(cudaMalloc(&base, total));
+  NVLLM_CUDA_OR_FAIL(cudaMemset(base, 0, total));
   if (ll_cap > 0) {  // "nothing has arrived" everywhere, before any peer can learn this region's handle
     ll_fill_kernel<<<256, 256>>>(reinterpret_cast<uint4*>(static_cast<uint8_t*>(base) + kSymCtrlBytes), 6 * ll_cap / 16);
-    NVLLM_CUDA(cudaGetLastError());
-    NVLLM_CUDA(cudaDeviceSynchronize());
+    NVLLM_CUDA_OR_FAIL(cudaGetLastError());
+    NVLLM_CUDA_OR_FAIL(cudaDeviceSynchronize());
   }
   cudaIpcMemHandle_t mine;
-  NVLLM_CUDA(cudaIpcGetMemHandle(&mine, base));
-  cudaIpcMemHandle_t* d_all = nullptr;
-  NVLLM_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_all), sizeof(mine) * (comm->world + 1)));
-  NVLLM_CUDA(cudaMemcpy(d_all + comm->world, &mine, sizeof(mine), cudaMemcpyHostToDevice));
-  cudaStream_t st;
-  NVLLM_CUDA(cudaStreamCreate(&st));
-  int rc = nccl_status(nccl().AllGather(d_all + comm->world, d_all, sizeof(mine), ncclUint8, comm->comm, st), "ncclAllGather(ipc)");
-  if (rc == 0) rc = cuda_status(cudaStreamSynchronize(st), "ipc all-gather");
-  cudaStreamDestroy(st);
+  NVLLM_CUDA_OR_FAIL(cudaIpcGetMemHandle(&mine, base));
+  NVLLM_CUDA_OR_FAIL(cudaMalloc(reinterpret_cast<void**>(&d_all), sizeof(mine) * (comm->world + 1)));
+  NVLLM_CUDA_OR_FAIL(cudaMemcpy(d_all + comm->world, &mine, sizeof(mine), cudaMemcpyHostToDevice));
+  NVLLM_CUDA_OR_FAIL(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  if (int rc = nccl_status(nccl().AllGather(d_all + comm->world, d_all, sizeof(mine), ncclUint8, comm->comm, st), "ncclAllGather(ipc)"))
+    return fail(rc);
+  if (int rc = stream_wait_bounded(st, "comm_symm_alloc: all-gather of the IPC handles")) {
+    stream_busy = rc == NVLLM_ERR_COMM;
+    return fail(rc);
+  }
   cudaIpcMemHandle_t all[8];
-  if (rc == 0) rc = cuda_status(cudaMemcpy(all, d_all, sizeof(mine) * comm->world, cudaMemcpyDeviceToHost), "ipc handles D2H");
-  cudaFree(d_all);
-  if (rc != 0) { cudaFree(base); return rc; }
+  NVLLM_CUDA_OR_FAIL(cudaMemcpy(all, d_all, sizeof(mine) * comm->world, cudaMemcpyDeviceToHost));
+  cudaStreamDestroy(st); st = nullptr;
+  cudaFree(d_all); d_all = nullptr;
   for (int r = 0; r < comm->world; ++r) {
-    if (r == comm->rank) { comm->sym_peer[r] = static_cast<uint8_t*>(base); continue; }
+    if (r == comm->rank) continue;
     void* pp = nullptr;
     cudaError_t e = cudaIpcOpenMemHandle(&pp, all[r], cudaIpcMemLazyEnablePeerAccess);
     if (e != cudaSuccess) {
       set_error("cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
-      cudaFree(base);
-      return NVLLM_ERR_COMM;
+      return fail(NVLLM_ERR_COMM);
     }
     comm->sym_peer[r] = static_cast<uint8_t*>(pp);
   }
   if (comm->h_err == nullptr) {
-    NVLLM_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&comm->h_err), sizeof(int), cudaHostAllocMapped));
-    *comm->h_err = 0;
-    NVLLM_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&comm->d_err), comm->h_err, 0));
+    NVLLM_CUDA_OR_FAIL(cudaHostAlloc(reinterpret_cast<void**>(&comm->h_err), 16 * sizeof(int), cudaHostAllocMapped));
+    memset(comm->h_err, 0, 16 * sizeof(int));
+    NVLLM_CUDA_OR_FAIL(cudaHostGetDevicePointer(reinterpret_cast<void**>(&comm->d_err), comm->h_err, 0));
   }
+#undef NVLLM_CUDA_OR_FAIL
+  comm->sym_peer[comm->rank] = static_cast<uint8_t*>(base);
   comm->sym_local = static_cast<uint8_t*>(base);
   comm->sym_bytes = total;
   comm->ll_cap = ll_cap;
@@ -804,8 +868,15 @@ int nvllmdbg_ar_timeline(unsigned long long* d_buf, unsigned int cap) {
 // 0, or NVLLM_ERR_COMM once a fused kernel of this communicator has given up waiting for a peer (sticky).
 int nvllm_comm_error(const nvllm_comm* comm) {
   if (comm == nullptr || comm->h_err == nullptr) return 0;
-  if (*reinterpret_cast<volatile int*>(comm->h_err) == 0) return 0;
-  nvllm::set_error("fused TP kernel: a peer rank did not arrive within NVLLM_COMM_TIMEOUT_MS (communicator is dead)");
+  volatile int* e = comm->h_err;
+  if (e[0] == 0) return 0;
+  static const char* const kPhase[] = {"?", "flag protocol: a peer's ready flag", "flag protocol: a peer's done flag",
+                                       "low-latency reduce: staged partial rows", "low-latency gather: normed rows"};
+  const int ph = e[1] >= 1 && e[1] <= 4 ? e[1] : 0;
+  nvllm::set_error("fused TP kernel on rank %d of %d gave up after NVLLM_COMM_TIMEOUT_MS waiting for %s (%s %d, CTA %d, %s %d, "
+                   "missing source ranks 0x%x); the communicator is dead",
+                   comm->rank, comm->world, kPhase[ph], ph <= 2 ? "peer" : "row", e[2], e[3], ph <= 2 ? "epoch" : "buffer pair",
+                   e[4], e[5]);
   return NVLLM_ERR_COMM;
 }
 
@@ -816,19 +887,35 @@ int nvllm_comm_destroy(nvllm_comm* comm) {
     if (r != comm->rank && comm->sym_peer[r]) cudaIpcCloseMemHandle(comm->sym_peer[r]);
   // Freeing exported memory while another process still has it mapped is undefined behaviour (observed as a hang at
   // process teardown): rendezvous once more — every rank has closed its peer mappings before anyone frees its region.
-  if (comm->sym_local && comm->comm && nvllm::nccl().ok && comm->world > 1) {
+  // The rendezvous is an NCCL all-reduce of one scratch word (never the live control block) with a host-side deadline.
+  // A communicator that already reported NVLLM_ERR_COMM has a peer that is gone or stuck: no rendezvous can complete, so
+  // none is tried, and — like after a rendezvous that timed out — the region is LEAKED (a peer may still have it mapped)
+  // and the NCCL communicator is aborted instead of destroyed (ncclCommDestroy waits for the peers too).
+  bool peers_ok = !(comm->h_err && *reinterpret_cast<volatile int*>(comm->h_err) != 0);
+  if (peers_ok && comm->sym_local && comm->comm && nvllm::nccl().ok && comm->world > 1) {
     cudaStream_t st = nullptr;
-    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess) {
-      nvllm::nccl().AllReduce(comm->sym_local, comm->sym_local, 1, nvllm::ncclFloat32, nvllm::ncclSum, comm->comm, st);
-      cudaStreamSynchronize(st);
-      cudaStreamDestroy(st);
+    float* word = nullptr;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess && cudaMalloc(reinterpret_cast<void**>(&word), 256) == cudaSuccess &&
+        cudaMemset(word, 0, 256) == cudaSuccess &&
+        nvllm::nccl().AllReduce(word, word, 1, nvllm::ncclFloat32, nvllm::ncclSum, comm->comm, st) == nvllm::ncclSuccess) {
+      peers_ok = nvllm::stream_wait_bounded(st, "comm_destroy: rendezvous before freeing the symmetric region") == 0;
+    } else {
+      peers_ok = false;
+    }
+    if (peers_ok) {  // a kernel that never finished may still touch them
+      if (word) cudaFree(word);
+      if (st) cudaStreamDestroy(st);
     }
   }
-  if (comm->sym_local) cudaFree(comm->sym_local);
-  if (comm->h_err) cudaFreeHost(comm->h_err);
-  if (comm->comm && nvllm::nccl().ok) nvllm::nccl().CommDestroy(comm->comm);
+  if (comm->sym_local && (peers_ok || comm->world == 1)) cudaFree(comm->sym_local);
+  if (comm->h_err && peers_ok) cudaFreeHost(comm->h_err);
+  if (comm->comm && nvllm::nccl().ok) {
+    if (peers_ok) nvllm::nccl().CommDestroy(comm->comm);
+    else if (nvllm::nccl().CommAbort) nvllm::nccl().CommAbort(comm->comm);
+  }
+  const int rc = peers_ok ? 0 : NVLLM_ERR_COMM;
   delete comm;
-  return 0;
+  return rc;
 }
 
 int nvllm_allreduce(nvllm_comm* comm, void* buf, size_t count, int32_t dtype, void* stream) {

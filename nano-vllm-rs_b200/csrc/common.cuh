@@ -68,7 +68,7 @@ struct Knobs {
   int ar_ll = 1;            // NVLLM_AR_LL: 0 = always the flag-protocol fused all-reduce (no low-latency push variant)
   long long ar_ll_max_bytes = 8ll << 20;  // NVLLM_AR_LL_MAX_BYTES: largest message of the low-latency variant (6x this is reserved)
   int profile = 0;          // NVLLM_PROFILE: 1 = the runner times every launch of eager steps with CUDA events
-  long long comm_timeout_ms = 600000;  // NVLLM_COMM_TIMEOUT_MS: peer-flag spin bound of the fused TP kernels
+  long long comm_timeout_ms = 20000;   // NVLLM_COMM_TIMEOUT_MS: how long a fused TP kernel (or a set-up / tear-down collective) waits for a peer
 };
 const Knobs& knobs();  // api.cu
 inline bool pdl_enabled() { return knobs().pdl != 0; }
