@@ -37,6 +37,7 @@ static void parse_knobs() {
     return (e && e[0]) ? atoi(e) : dflt;
   };
   k.pdl = num("NVLLM_PDL", 1) != 0;
+  k.pdl_tp = num("NVLLM_PDL_TP", 0) != 0;
   k.gemm_bn = num("NVLLM_GEMM_BN", 0);
   k.gemm_2cta = num("NVLLM_GEMM_2CTA", 1);
   k.gemm_mcast = num("NVLLM_GEMM_MCAST", 0) == 1;
@@ -60,6 +61,8 @@ static void parse_knobs() {
   if (const char* e = getenv("NVLLM_COMM_TIMEOUT_MS")) { const long long v = atoll(e); if (v > 0) k.comm_timeout_ms = v; }
   g_knobs = k;
 }
+
+std::atomic<int> g_live_symm_regions{0};
 
 const Knobs& knobs() {
   std::call_once(g_knobs_once, parse_knobs);

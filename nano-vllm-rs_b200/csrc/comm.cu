@@ -196,8 +196,8 @@ allreduce_add_rmsnorm_kernel(const FusedArParams p) {
   pdl_launch_dependents();
   pdl_wait();
   uint32_t* ctrl = reinterpret_cast<uint32_t*>(p.self);
-  const uint32_t epoch = ctrl[129] + 1;  // +516 bytes; written only by this rank's last CTA of the previous call
-  const bool dead = ctrl[130] != 0;      // a previous call timed out: never wait again (the host reports the error)
+  const uint32_t epoch = ld_state(ctrl + 129) + 1;  // +516 bytes; written only by this rank's last CTA of the previous call
+  const bool dead = ld_state(ctrl + 130) != 0;  // a previous call timed out: never wait again (the host reports the error)
   if (blockIdx.x == 0 && threadIdx.x < WORLD) {
     __threadfence_system();
     st_release_sys(reinterpret_cast<uint32_t*>(peer_of(p, threadIdx.x)) + p.rank, epoch);  // ready[rank] on peer
@@ -374,11 +374,11 @@ allreduce_add_rmsnorm_ll_kernel(const LLArParams p) {
   pdl_wait();
   ATL(1);
   uint32_t* ctrl = reinterpret_cast<uint32_t*>(p.self);
-  const uint32_t b = ctrl[131];                          // pair of this call; advanced by the last CTA of the call
+  const uint32_t b = ld_state(ctrl + 131);                  // pair of this call; advanced by the last CTA of the call
   const uint32_t bclr = b >= 1 ? b - 1 : 2;              // (b + 2) % 3
-  const uint32_t clr_bytes = ctrl[132 + bclr];           // what the last call on that pair used
+  const uint32_t clr_bytes = ld_state(ctrl + 132 + bclr);   // what the last call on that pair used
   uint32_t* dead_p = ctrl + 130;
-  const bool dead = *dead_p != 0;
+  const bool dead = ld_state(dead_p) != 0;
   const int R = (p.num_tokens + WORLD - 1) / WORLD;      // rows per owner
   const size_t row_bytes = static_cast<size_t>(p.hidden) * 2;
   const size_t stage_off = p.ll_off + static_cast<size_t>(b) * 2 * p.ll_cap;
@@ -753,6 +753,7 @@ int nvllm_comm_symm_alloc(nvllm_comm* comm, size_t bytes, void** local_base) {
 #undef NVLLM_CUDA_OR_FAIL
   comm->sym_peer[comm->rank] = static_cast<uint8_t*>(base);
   comm->sym_local = static_cast<uint8_t*>(base);
+  g_live_symm_regions.fetch_add(1, std::memory_order_relaxed);  // from here on kernels launch without PDL (common.cuh)
   comm->sym_bytes = total;
   comm->ll_cap = ll_cap;
   comm->user_off = user_off;
@@ -891,6 +892,7 @@ int nvllm_comm_destroy(nvllm_comm* comm) {
   // A communicator that already reported NVLLM_ERR_COMM has a peer that is gone or stuck: no rendezvous can complete, so
   // none is tried, and — like after a rendezvous that timed out — the region is LEAKED (a peer may still have it mapped)
   // and the NCCL communicator is aborted instead of destroyed (ncclCommDestroy waits for the peers too).
+  if (comm->sym_local) nvllm::g_live_symm_regions.fetch_sub(1, std::memory_order_relaxed);
   bool peers_ok = !(comm->h_err && *reinterpret_cast<volatile int*>(comm->h_err) != 0);
   if (peers_ok && comm->sym_local && comm->comm && nvllm::nccl().ok && comm->world > 1) {
     cudaStream_t st = nullptr;

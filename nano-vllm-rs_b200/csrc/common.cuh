@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "../../include/nvllm.h"
@@ -51,6 +52,8 @@ int sm_count();  // api.cu (cached)
 // path.  nvllm_reload_env() (benchmark tools that sweep knobs inside one process) re-parses them.
 struct Knobs {
   int pdl = 1;              // NVLLM_PDL: 0 disables programmatic dependent launch
+  int pdl_tp = 0;           // NVLLM_PDL_TP: 1 keeps programmatic dependent launch while a TP symmetric region is live (round-2
+                            // behaviour: ~1 in 10 tiny-model runs at 8 ranks ends with rank 0 one call behind)
   int gemm_bn = 0;          // NVLLM_GEMM_BN: forced tile width (0 = heuristic)
   int gemm_2cta = 1;        // NVLLM_GEMM_2CTA: 0 never, 1 default (M > 512), 2 every M > 128
   int gemm_mcast = 0;       // NVLLM_GEMM_MCAST: 1 enables the x-multicast clusters
@@ -71,7 +74,14 @@ struct Knobs {
   long long comm_timeout_ms = 20000;   // NVLLM_COMM_TIMEOUT_MS: how long a fused TP kernel (or a set-up / tear-down collective) waits for a peer
 };
 const Knobs& knobs();  // api.cu
-inline bool pdl_enabled() { return knobs().pdl != 0; }
+extern std::atomic<int> g_live_symm_regions;  // api.cu; nvllm_comm_symm_alloc ++, nvllm_comm_destroy --
+// Programmatic dependent launch is OFF while this process holds a tensor-parallel symmetric region, unless NVLLM_PDL_TP=1:
+// with it on, the fused all-reduce kernels' per-call device state (buffer pair / epoch, handed from one call to the next
+// through the control block) was observed one call stale on the rank whose kernels never spin (8 ranks, 4-CTA grids, about
+// one run in ten; tools/tp_parity_soak.py); with it off, 50 consecutive runs were clean.  Root cause open.
+inline bool pdl_enabled() {
+  return knobs().pdl != 0 && (knobs().pdl_tp != 0 || g_live_symm_regions.load(std::memory_order_relaxed) == 0);
+}
 
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) exactly once per kernel instantiation, safe under concurrent callers
 // (the header promises re-entrancy).  Use inside a function that returns the C-ABI status code.
@@ -99,6 +109,17 @@ namespace nvllm {
 // then pdl_wait() before the first access to anything a previous kernel wrote or still reads.
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+// A word of per-communicator device state that ONE CTA of an earlier kernel rewrites and EVERY CTA of a later kernel reads
+// (call counters, buffer-pair index, dead flag in the symmetric region's control block).  Read it past L1: with
+// programmatic dependent launch a CTA of the later kernel can be resident on an SM (launched early, parked in
+// griddepcontrol.wait) BEFORE a CTA of the earlier kernel on the same SM pulls the old value of the line into that SM's
+// L1 — the later kernel's ordinary ld.global then hits the stale line.  Observed as a rank that re-used the previous
+// call's buffer pair / epoch (the round-2 8-GPU hang); a gpu-scope load always goes to L2.
+__device__ __forceinline__ uint32_t ld_state(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
@@ -160,7 +181,7 @@ __device__ __forceinline__ bf16* push_row(const RowPush& ps, int row) {
   uint8_t* base = ps.peer[0];
 #pragma unroll
   for (int i = 1; i < 8; ++i) base = (owner == i) ? ps.peer[i] : base;  // no run-time index into the parameter block
-  const uint32_t b = ps.ctrl[131];
+  const uint32_t b = ld_state(ps.ctrl + 131);
   return reinterpret_cast<bf16*>(base + ps.ll_off + static_cast<size_t>(b) * 2 * ps.ll_cap +
                                  (static_cast<size_t>(ps.rank) * ps.R + (row - owner * ps.R)) * ps.hidden * 2);
 }
