@@ -46,7 +46,9 @@ const char* nvllm_last_error(void);
 /* 1 when a CUDA device of compute capability 10.x is visible, else 0 (never throws). */
 int nvllm_device_ok(void);
 /* The NVLLM_* environment knobs (A/B measurement switches) are parsed once per process, never on a
- * dispatch path; benchmark tools that sweep a knob inside one process call this after changing the environment. */
+ * dispatch path; benchmark tools that sweep a knob inside one process call this after changing the environment.
+ * NOT re-entrant, unlike every other entry point: it rewrites the knob set in place, so call it only while no other thread
+ * is inside the library (a dispatch running concurrently could see half of the old set and half of the new). */
 int nvllm_reload_env(void);
 
 /* ------------------------------------------------------------------------------------------------

@@ -121,7 +121,7 @@ struct nvllm_runner {
   std::vector<cudaEvent_t> prof_pool;
   std::map<std::string, std::pair<double, int64_t>> prof_acc;  // name -> (total us, launches)
   bool fuse_rope = false; // NVLLM_FUSE_ROPE=1: qkv GEMM epilogue does q/k norm + RoPE + KV store for decode-sized batches
-  bool fuse_decode = true; // decode: q/k-norm + RoPE + KV store inside the paged attention kernel (NVLLM_FUSE_DECODE=0: separate)
+  bool fuse_decode = false; // NVLLM_FUSE_DECODE=1 (opt-in, measured slower): q/k-norm + RoPE + KV store inside the paged attention kernel
   bool fused_tp = false;  // h / normed / proj live in NVLink-mapped symmetric memory; all-reduce fused with add + RMSNorm
 
   ~nvllm_runner() {
