@@ -263,10 +263,8 @@ int nvllm_runner::create(const nvllm_config& c, nvllm_comm* cm) {
   RUN(dalloc(&gate_up, T * 2 * inter)); RUN(dalloc(&act, T * inter));
   RUN(dalloc(&last_hidden, static_cast<size_t>(max_seqs) * hidden));
   RUN(dalloc(&logits, static_cast<size_t>(max_seqs) * vshard));
-  if (tp > 1) {
-    RUN(dalloc(&gathered_logits, static_cast<size_t>(max_seqs) * vocab));
-    RUN(dalloc(&full_logits, static_cast<size_t>(max_seqs) * vocab));
-  }
+  // gathered_logits / full_logits (tp > 1, 2 x max_seqs x vocab f32 = 2 x 311 MB at 512 x 151936) are taken on the first
+  // SAMPLED batch (sample() below): greedy-only serving, the benchmarked TP configuration included, never pays for them.
   RUN(dalloc(&tokens, max_seqs)); RUN(dalloc(&local_ids, max_seqs)); RUN(dalloc(&local_max, max_seqs));
   RUN(dalloc(&all_ids, static_cast<size_t>(max_seqs) * tp)); RUN(dalloc(&all_max, static_cast<size_t>(max_seqs) * tp));
   // split-K workspace: the largest any decode bucket can ask for
@@ -645,6 +643,11 @@ int nvllm_runner::sample(const nvllm_batch& b) {
   NVLLM_CUDA(cudaMemcpyAsync(d_samp, h_samp, 24 * S, cudaMemcpyHostToDevice, stream));
   ++last_launches;
   if (tp > 1) {
+    if (gathered_logits == nullptr) {  // first sampled batch: every rank gets here in the same step (same batches everywhere);
+      // outside any graph capture (sampling runs after the decode graph), one-time cudaMalloc device synchronisation
+      RUN(dalloc(&gathered_logits, static_cast<size_t>(max_seqs) * vocab));
+      RUN(dalloc(&full_logits, static_cast<size_t>(max_seqs) * vocab));
+    }
     // Vocab-sharded head (embed_head.rs:321-336 TODO): all-gather the f32 shards, put the rows back together, and run the
     // SAME deterministic sampler on the full rows on every rank — identical tokens everywhere, no token broadcast.
     RUN(nvllm_allgather(comm, logits, gathered_logits, sizeof(float) * n * vshard, stream));
