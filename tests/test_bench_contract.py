@@ -49,3 +49,20 @@ def test_workload_windows_follow_the_baseline_configs():
     model, wl, prompt, K, W = bench.workload(args)
     assert wl["seqs"] == 64 and wl["blocks_per_seq"] == 129
     assert "decode" in base["metric"] or "token" in base["metric"]              # the metric bench.py prints is BASELINE.json's
+
+
+def test_watchdog_names_the_stalled_phase_on_stdout():
+    """A phase that outlasts BENCH_WATCHDOG_S ends the process with status 3 and ONE JSON line on stdout that names the last
+    progress message — the round-2 8-GPU run hung for 870 s and left nothing in the driver's record; this is what it would
+    have left.  progress() re-arms the timer: a run made of many short phases is never cut."""
+    code = ("import sys, time; sys.path.insert(0, %r); import bench; bench.arm_watchdog()\n"
+            "for i in range(4):\n    time.sleep(0.7); bench.progress('short phase %%d' %% i)\n"
+            "bench.progress('the phase that hangs'); time.sleep(30)\n") % ROOT
+    env = dict(os.environ, BENCH_WATCHDOG_S="1.5", RANK="3", WORLD_SIZE="8")
+    p = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=60)
+    assert p.returncode == 3, (p.returncode, p.stderr[-1500:])
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["error"] == "watchdog" and d["phase"] == "the phase that hangs" and d["rank"] == 3 and d["n_gpus"] == 8
+    assert d["stalled_s"] >= 1.5 and "short phase 3" in p.stderr and "Thread" in p.stderr  # stacks went to stderr
