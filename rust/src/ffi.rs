@@ -83,6 +83,20 @@ impl Attention {
         }
     }
 
+    /// The decode branch of `forward` for a host that has no device allocator to give it a workspace (a plugin hook that
+    /// only sees one op's tensors, a pool sealed after start-up): the split-K partials live in an 8 MiB array inside
+    /// libnvllm.so.  No counterpart in the reference.  Errors with NVLLM_ERR_WORKSPACE when the batch needs more than
+    /// `nvllm_paged_decode_static_scratch_bytes()`; call it once during set-up (before any stream capture), and never from
+    /// two streams at once — all calls on a GPU share the array.  The KV store of this step must already have happened.
+    #[allow(clippy::too_many_arguments)]
+    pub unsafe fn forward_decode_no_alloc(&self, out: *mut c_void, q: *const c_void, qkv_stride: i64, k_cache: *const c_void,
+                                          v_cache: *const c_void, ctx: &AttnContext, stream: *mut c_void) -> anyhow::Result<()> {
+        let hd = self.num_heads as i64 * self.head_dim as i64;
+        check(nvllm_paged_decode_attention_static(out, q, k_cache, v_cache, ctx.block_tables, ctx.context_lens, ctx.num_seqs,
+                                                  self.num_heads, ctx.max_blocks, qkv_stride, hd, &self.layout, self.scale,
+                                                  0, NVLLM_BF16, stream))
+    }
+
     /// Bytes `forward` may need in `workspace` for a decode batch (split-K partials).
     pub fn decode_workspace_bytes(&self, max_batch: i32) -> usize {
         unsafe { nvllm_paged_decode_workspace_bytes(max_batch, self.num_heads, self.head_dim, 0) }
