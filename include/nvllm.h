@@ -12,6 +12,8 @@
  *   - the caller owns every buffer (inputs, outputs, KV cache, workspace) and the stream; kernels
  *     never allocate, free or synchronise and keep no global state, so every call is legal inside
  *     CUDA-graph capture.  Pointers are device pointers unless the name starts with `h_`.
+ *     (Stated exceptions: nvllm_paged_decode_attention_static owns a per-GPU scratch array and is outside this
+ *     paragraph's promises — read its own comment; nvllm_reload_env is not re-entrant; nvllm_comm_* are collectives.)
  *   - activations / weights / KV cache are bf16 (NVLLM_BF16); accumulation is fp32.
  *   - strides are in ELEMENTS.  The innermost (head_dim) dimension is always contiguous and every
  *     row start must be 16-byte aligned.
